@@ -1,0 +1,140 @@
+"""Programmatic protobuf descriptors + gRPC plumbing for the ParameterServer service.
+
+Replaces the reference's generated modules (reference: src/communication/ps_pb2.py,
+src/communication/ps_pb2_grpc.py, regenerate_proto.sh) without needing protoc:
+the FileDescriptorProto is assembled with ``descriptor_pb2`` and registered in a
+*private* DescriptorPool, so this module can live in the same process as the
+reference's own ``ps_pb2`` (needed by the wire-compat tests) without a duplicate
+symbol clash in the default pool.
+
+Public surface mirrors the generated code:
+  RegisterRequest/RegisterReply/PushRequest/PushReply/FetchRequest/FetchReply/
+  JobFinishedRequest/JobFinishedReply  (message classes)
+  ParameterServerStub(channel)                      (ps_pb2_grpc.py:28)
+  ParameterServerServicer                           (ps_pb2_grpc.py:60)
+  add_ParameterServerServicer_to_server(svc, srv)   (ps_pb2_grpc.py:95)
+"""
+from __future__ import annotations
+
+import grpc
+from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
+
+SERVICE_NAME = "ParameterServer"          # no proto package -> '/ParameterServer/<Method>'
+_F = descriptor_pb2.FieldDescriptorProto
+
+# (message, [(field, number, type)])
+_MESSAGES = [
+    ("RegisterRequest", [("worker_ip", 1, _F.TYPE_STRING)]),
+    ("RegisterReply", [("worker_id", 1, _F.TYPE_INT32), ("total_workers", 2, _F.TYPE_INT32)]),
+    ("PushRequest", [("worker_id", 1, _F.TYPE_INT32), ("gradients", 2, _F.TYPE_BYTES),
+                     ("local_step", 3, _F.TYPE_INT32)]),
+    ("PushReply", [("received", 1, _F.TYPE_BOOL)]),
+    ("FetchRequest", [("worker_id", 1, _F.TYPE_INT32)]),
+    ("FetchReply", [("parameters", 1, _F.TYPE_BYTES), ("global_step", 2, _F.TYPE_INT32)]),
+    ("JobFinishedRequest", [("worker_id", 1, _F.TYPE_INT32)]),
+    ("JobFinishedReply", [("message", 1, _F.TYPE_STRING)]),
+]
+
+# (method, request, reply) -- note the misspelt PushGradrients: it is the wire name.
+METHODS = [
+    ("RegisterWorker", "RegisterRequest", "RegisterReply"),
+    ("PushGradrients", "PushRequest", "PushReply"),
+    ("FetchParameters", "FetchRequest", "FetchReply"),
+    ("JobFinished", "JobFinishedRequest", "JobFinishedReply"),
+]
+
+
+def build_file_descriptor_proto() -> descriptor_pb2.FileDescriptorProto:
+    fdp = descriptor_pb2.FileDescriptorProto()
+    fdp.name = "dps_b200/ps.proto"
+    fdp.syntax = "proto3"
+    for mname, fields in _MESSAGES:
+        m = fdp.message_type.add()
+        m.name = mname
+        for fname, num, ftype in fields:
+            f = m.field.add()
+            f.name, f.number, f.type = fname, num, ftype
+            f.label = _F.LABEL_OPTIONAL
+    svc = fdp.service.add()
+    svc.name = SERVICE_NAME
+    for meth, req, rep in METHODS:
+        md = svc.method.add()
+        md.name, md.input_type, md.output_type = meth, "." + req, "." + rep
+    return fdp
+
+
+_POOL = descriptor_pool.DescriptorPool()
+_FILE = _POOL.AddSerializedFile(build_file_descriptor_proto().SerializeToString())
+_CLASSES = {name: message_factory.GetMessageClass(_POOL.FindMessageTypeByName(name))
+            for name, _ in _MESSAGES}
+
+RegisterRequest = _CLASSES["RegisterRequest"]
+RegisterReply = _CLASSES["RegisterReply"]
+PushRequest = _CLASSES["PushRequest"]
+PushReply = _CLASSES["PushReply"]
+FetchRequest = _CLASSES["FetchRequest"]
+FetchReply = _CLASSES["FetchReply"]
+JobFinishedRequest = _CLASSES["JobFinishedRequest"]
+JobFinishedReply = _CLASSES["JobFinishedReply"]
+
+# 500 MB messages + keepalive, as the reference (server.py:372-378, worker.py:203-209).
+GRPC_OPTIONS = [
+    ("grpc.max_receive_message_length", 500 * 1024 * 1024),
+    ("grpc.max_send_message_length", 500 * 1024 * 1024),
+    ("grpc.keepalive_time_ms", 30000),
+    ("grpc.keepalive_timeout_ms", 5000),
+    ("grpc.keepalive_permit_without_calls", True),
+]
+
+
+def method_path(method: str) -> str:
+    return f"/{SERVICE_NAME}/{method}"
+
+
+class ParameterServerStub:
+    """Client stub; one unary-unary callable per RPC (same attribute names as generated code)."""
+
+    def __init__(self, channel: grpc.Channel):
+        for meth, req, rep in METHODS:
+            setattr(self, meth, channel.unary_unary(
+                method_path(meth),
+                request_serializer=_CLASSES[req].SerializeToString,
+                response_deserializer=_CLASSES[rep].FromString,
+            ))
+
+
+class ParameterServerServicer:
+    """Abstract service; subclasses override the four RPC methods."""
+
+    def _unimplemented(self, context):
+        context.set_code(grpc.StatusCode.UNIMPLEMENTED)
+        context.set_details("Method not implemented!")
+        raise NotImplementedError("Method not implemented!")
+
+    def RegisterWorker(self, request, context):
+        self._unimplemented(context)
+
+    def PushGradrients(self, request, context):
+        self._unimplemented(context)
+
+    def FetchParameters(self, request, context):
+        self._unimplemented(context)
+
+    def JobFinished(self, request, context):
+        self._unimplemented(context)
+
+
+def add_ParameterServerServicer_to_server(servicer, server: grpc.Server) -> None:
+    handlers = {}
+    for meth, req, rep in METHODS:
+        handlers[meth] = grpc.unary_unary_rpc_method_handler(
+            getattr(servicer, meth),
+            request_deserializer=_CLASSES[req].FromString,
+            response_serializer=_CLASSES[rep].SerializeToString,
+        )
+    server.add_generic_rpc_handlers(
+        (grpc.method_handlers_generic_handler(SERVICE_NAME, handlers),))
+
+
+def make_channel(address: str) -> grpc.Channel:
+    return grpc.insecure_channel(address, options=GRPC_OPTIONS)

@@ -1,0 +1,428 @@
+"""CPU / remote parameter-server role served over gRPC.
+
+This is the control-plane and slow-path twin of the on-box sharded store
+(``dps_b200.store`` + the sm_100a push/pull kernels).  It reproduces the
+behaviour of the reference servicer (reference: src/parameter_server/server.py:81-368)
+with the defects listed in SURVEY §2.6 fixed behind flags:
+
+  Q1  sync push is a *true* barrier by default (``nonblocking_sync=True`` restores the
+      reference's return-immediately behaviour, server.py:264-288)
+  Q2  the barrier counts distinct worker ids per round, not arrivals
+  Q3  the barrier times out (``barrier_timeout_s``) and proceeds with the ranks present
+  Q4  SGD has optional momentum / weight decay (0/0 == reference, server.py:133)
+  Q5  BN running statistics can be maintained (``bn_buffer_policy``)
+  Q8  the staleness bound is honoured as configured
+  Q9  staleness statistics are running mean / max / histogram, not last-value-only
+  Q10 worker ids are re-slotted instead of growing without bound
+  Q11 SERVER_FINAL_METRICS is emitted exactly once (stdout + optional file)
+  Q15 payloads are DPS1 frames; pickles only via the restricted unpickler
+  Q16 every shared counter is mutated under a lock
+"""
+from __future__ import annotations
+
+import json
+import threading
+import time
+from collections import deque
+from concurrent import futures
+from typing import Dict, List, Optional
+
+import grpc
+import numpy as np
+
+from ..config import Config
+from ..utils import metrics as M
+from . import codec, proto
+
+
+def staleness_weight(staleness: int, alpha: float = 0.1, floor: float = 0.1) -> float:
+    """max(floor, 1/(1+alpha*s))  (reference: server.py:178)."""
+    return max(floor, 1.0 / (1.0 + staleness * alpha))
+
+
+class HostOptimizer:
+    """fp32 SGD(+momentum, +weight decay) over a dict of numpy arrays, in place.
+
+    momentum=0, weight_decay=0 is bit-for-bit ``p = p - lr*g`` (reference: server.py:126-143).
+    """
+
+    def __init__(self, params: Dict[str, np.ndarray], lr: float, momentum: float = 0.0,
+                 weight_decay: float = 0.0):
+        self.params = params
+        self.lr, self.momentum, self.weight_decay = float(lr), float(momentum), float(weight_decay)
+        self.velocity: Dict[str, np.ndarray] = {}
+
+    def step(self, grads: Dict[str, np.ndarray], scale: float = 1.0) -> None:
+        for name, g in grads.items():
+            p = self.params.get(name)
+            if p is None or not np.issubdtype(p.dtype, np.floating):
+                continue
+            g = np.asarray(g, dtype=np.float32)
+            if scale != 1.0:
+                g = g * np.float32(scale)
+            if self.weight_decay:
+                g = g + np.float32(self.weight_decay) * p
+            if self.momentum:
+                v = self.velocity.get(name)
+                if v is None:
+                    v = self.velocity[name] = np.array(g, dtype=np.float32, copy=True)
+                else:
+                    v *= np.float32(self.momentum)
+                    v += g
+                g = v
+            # written as p - lr*g (not p -= ...) so fp32 rounding matches the reference exactly
+            self.params[name] = p - np.float32(self.lr) * g
+
+
+def mean_gradients(grad_sets: List[Dict[str, np.ndarray]]) -> Dict[str, np.ndarray]:
+    """Element-wise mean over worker gradient dicts (reference: server.py:145-169)."""
+    if not grad_sets:
+        return {}
+    out: Dict[str, np.ndarray] = {}
+    for name in grad_sets[0].keys():
+        acc, n = None, 0
+        for gs in grad_sets:
+            g = gs.get(name)
+            if g is None:
+                continue
+            acc = g.astype(np.float32, copy=True) if acc is None else acc + g
+            n += 1
+        if n:
+            out[name] = acc / np.float32(n)
+    return out
+
+
+class ParameterServerServicer(proto.ParameterServerServicer):
+    """gRPC servicer. Constructor keeps the reference's positional signature (server.py:84)."""
+
+    def __init__(self, mode: str = "sync", total_workers: int = 4, learning_rate: float = 0.1,
+                 staleness_bound: int = 5, config: Optional[Config] = None,
+                 initial_state: Optional[Dict[str, np.ndarray]] = None, verbose: bool = False):
+        cfg = (config or Config()).replace(mode=mode, workers=total_workers, lr=learning_rate,
+                                           staleness_bound=staleness_bound).validate()
+        self.cfg = cfg
+        self.mode, self.total_workers = cfg.mode, cfg.workers
+        self.learning_rate, self.staleness_bound = cfg.lr, cfg.staleness_bound
+        self.verbose = verbose
+
+        if initial_state is None:
+            from ..models.resnet import build_model
+            model = build_model(cfg.num_classes, seed=cfg.seed)
+            initial_state = {k: v.detach().cpu().numpy() for k, v in model.state_dict().items()}
+        self.parameters: Dict[str, np.ndarray] = {k: np.array(v, copy=True) for k, v in initial_state.items()}
+        self.param_lock = threading.Lock()
+        self.opt = HostOptimizer(self.parameters, cfg.lr, cfg.momentum, cfg.weight_decay)
+
+        # membership
+        self.registration_lock = threading.Lock()
+        self.registered_workers: Dict[int, dict] = {}
+        self.registered_workers_count = 0
+        self.active_workers: set = set()
+        self._free_ids: List[int] = []
+        self.membership_epoch = 0
+
+        # training state
+        self.global_step = 0
+        self.total_updates = 0
+        self.gradients_processed = 0
+        self.stats_lock = threading.Lock()
+
+        # sync barrier
+        self.sync_cv = threading.Condition()
+        self.round_id = 0
+        self.pending_gradients: Dict[int, Dict[str, np.ndarray]] = {}
+        self.pending_buffers: Dict[int, Dict[str, np.ndarray]] = {}
+        self.round_started_at: Optional[float] = None
+        self.barrier_timeouts = 0
+
+        # async stats (Q9)
+        self.async_updates = 0
+        self.rejected_updates = 0
+        self.gradient_staleness: Dict[int, int] = {}       # last value per worker (reference field)
+        self.staleness_sum = 0
+        self.staleness_max = 0
+        self.staleness_hist: Dict[int, int] = {}
+
+        self.update_times = deque(maxlen=100)
+        self.start_time = time.time()
+        self._fetch_cache: Dict[bool, tuple] = {}
+        self._final_emitted = False
+        self.final_metrics: Optional[dict] = None
+
+    # ------------------------------------------------------------------ numerics
+    def apply_gradients(self, grads: Dict[str, np.ndarray], scale: float = 1.0) -> None:
+        t0 = time.time()
+        with self.param_lock:
+            self.opt.step(grads, scale)
+            self.global_step += 1
+            self.total_updates += 1
+            self._fetch_cache.clear()
+        self.update_times.append(time.time() - t0)
+
+    def aggregate_gradients_sync(self, worker_gradients: List[Dict[str, np.ndarray]]):
+        return mean_gradients(worker_gradients)
+
+    def apply_gradients_async(self, grads: Dict[str, np.ndarray], worker_id: int, staleness: int) -> bool:
+        if staleness > self.staleness_bound:
+            with self.stats_lock:
+                self.rejected_updates += 1
+            return False
+        w = staleness_weight(staleness, self.cfg.staleness_alpha, self.cfg.staleness_floor)
+        self.apply_gradients(grads, scale=w)
+        with self.stats_lock:
+            self.async_updates += 1
+        return True
+
+    def decompress_gradients(self, grads):
+        return codec.decompress_gradients(grads)
+
+    # ------------------------------------------------------------------ RPCs
+    def RegisterWorker(self, request, context):
+        with self.registration_lock:
+            if self._free_ids:
+                wid = self._free_ids.pop(0)
+            elif self.registered_workers_count < self.total_workers:
+                wid = self.registered_workers_count
+                self.registered_workers_count += 1
+            else:
+                if context is not None:
+                    context.abort(grpc.StatusCode.RESOURCE_EXHAUSTED,
+                                  f"all {self.total_workers} worker slots are taken")
+                raise RuntimeError("all worker slots are taken")
+            now = time.time()
+            self.registered_workers[wid] = {"worker_id": wid, "worker_ip": request.worker_ip,
+                                            "registered_at": now, "last_seen": now}
+            self.active_workers.add(wid)
+            self.membership_epoch += 1
+        self._log(f"[RegisterWorker] Worker {wid} from {request.worker_ip} registered "
+                  f"({len(self.active_workers)}/{self.total_workers})")
+        return proto.RegisterReply(worker_id=wid, total_workers=self.total_workers)
+
+    def _touch(self, wid: int) -> None:
+        with self.registration_lock:
+            info = self.registered_workers.get(wid)
+            if info is not None:
+                info["last_seen"] = time.time()
+
+    def FetchParameters(self, request, context):
+        self._touch(request.worker_id)
+        as_pickle = bool(self.cfg.compat_pickle)
+        with self.param_lock:
+            cached = self._fetch_cache.get(as_pickle)
+            if cached is None or cached[0] != self.global_step:
+                payload = codec.encode_any(self.parameters, as_pickle, {"global_step": self.global_step})
+                cached = (self.global_step, payload)
+                self._fetch_cache[as_pickle] = cached
+            step, payload = cached
+        return proto.FetchReply(parameters=payload, global_step=step)
+
+    def PushGradrients(self, request, context):
+        wid, local_step = request.worker_id, request.local_step
+        try:
+            tensors, meta = codec.decode_any(request.gradients, allow_pickle=self.cfg.compat_pickle)
+        except Exception as e:  # malformed payload == reference's received=False path (server.py:260-262)
+            self._log(f"Error processing gradients from worker {wid}: {e}")
+            return proto.PushReply(received=False)
+        buffers = {k[len("buffer/"):]: np.asarray(v) for k, v in tensors.items() if k.startswith("buffer/")}
+        grads = self.decompress_gradients({k: v for k, v in tensors.items() if not k.startswith("buffer/")})
+        with self.stats_lock:
+            self.gradients_processed += 1
+        self._touch(wid)
+        if self.mode == "sync":
+            ok = self._handle_sync_gradients(wid, grads, local_step, buffers)
+        else:
+            ok = self._handle_async_gradients(wid, grads, local_step, buffers)
+        return proto.PushReply(received=ok)
+
+    # sync -----------------------------------------------------------------
+    def _expected(self) -> int:
+        return self.total_workers
+
+    def _complete_round_locked(self) -> None:
+        sets = list(self.pending_gradients.values())
+        agg = self.aggregate_gradients_sync(sets)
+        if agg:
+            self.apply_gradients(agg)
+        self._merge_buffers(list(self.pending_buffers.values()))
+        self.pending_gradients.clear()
+        self.pending_buffers.clear()
+        self.round_started_at = None
+        self.round_id += 1
+        self.sync_cv.notify_all()
+
+    def _handle_sync_gradients(self, wid, grads, local_step, buffers=None) -> bool:
+        with self.sync_cv:
+            my_round = self.round_id
+            if not self.pending_gradients:
+                self.round_started_at = time.time()
+            self.pending_gradients[wid] = grads            # Q2: keyed by id; completion counts ids
+            if buffers:
+                self.pending_buffers[wid] = buffers
+            if len(self.pending_gradients) >= self._expected():
+                self._complete_round_locked()
+                return True
+            if self.cfg.nonblocking_sync:                   # Q1 compat: reference never blocks
+                return True
+            deadline = (self.round_started_at or time.time()) + self.cfg.barrier_timeout_s
+            while self.round_id == my_round:
+                left = deadline - time.time()
+                if left <= 0:                               # Q3: proceed with the ranks present
+                    if self.round_id == my_round:
+                        self.barrier_timeouts += 1
+                        self.membership_epoch += 1
+                        self._log(f"sync barrier timed out with {len(self.pending_gradients)}/"
+                                  f"{self._expected()} workers; proceeding")
+                        self._complete_round_locked()
+                    break
+                self.sync_cv.wait(timeout=left)
+            return True
+
+    # async ----------------------------------------------------------------
+    def _handle_async_gradients(self, wid, grads, local_step, buffers=None) -> bool:
+        with self.param_lock:
+            staleness = self.global_step - local_step       # Q6: read under the lock
+        ok = self.apply_gradients_async(grads, wid, staleness)
+        if ok and buffers:
+            self._merge_buffers([buffers], ema=1.0 / max(1, self.total_workers))
+        with self.stats_lock:
+            self.gradient_staleness[wid] = staleness
+            self.staleness_sum += max(0, staleness)
+            self.staleness_max = max(self.staleness_max, staleness)
+            self.staleness_hist[staleness] = self.staleness_hist.get(staleness, 0) + 1
+        return ok
+
+    # BN buffers (Q5) --------------------------------------------------------
+    def _merge_buffers(self, buffer_sets: List[Dict[str, np.ndarray]], ema: Optional[float] = None) -> None:
+        if not buffer_sets or self.cfg.bn_buffer_policy == "reference":
+            return
+        with self.param_lock:
+            for name in buffer_sets[0].keys():
+                cur = self.parameters.get(name)
+                if cur is None:
+                    continue
+                vals = [bs[name] for bs in buffer_sets if name in bs]
+                if np.issubdtype(cur.dtype, np.integer):
+                    self.parameters[name] = np.maximum(cur, np.max(np.stack(vals), axis=0)).astype(cur.dtype)
+                    continue
+                mean = np.mean(np.stack([v.astype(np.float32) for v in vals]), axis=0)
+                if ema is None:
+                    self.parameters[name] = mean.astype(cur.dtype)
+                else:
+                    self.parameters[name] = ((1.0 - ema) * cur + ema * mean).astype(cur.dtype)
+            self._fetch_cache.clear()
+
+    # finish ---------------------------------------------------------------
+    def JobFinished(self, request, context):
+        wid = request.worker_id
+        emit = False
+        with self.registration_lock:
+            if wid in self.active_workers:
+                self.active_workers.discard(wid)
+                self._free_ids.append(wid)
+                self._free_ids.sort()
+                self.membership_epoch += 1
+            if not self.active_workers and not self._final_emitted:
+                self._final_emitted = emit = True
+        if emit:
+            self._print_final_statistics()
+        return proto.JobFinishedReply(message="Acknowledged")
+
+    # liveness -------------------------------------------------
+    def stale_workers(self, older_than_s: float) -> List[int]:
+        now = time.time()
+        with self.registration_lock:
+            return [w for w in self.active_workers
+                    if now - self.registered_workers[w]["last_seen"] > older_than_s]
+
+    def evict(self, wid: int) -> None:
+        """Drop a dead worker: frees its id/partition for re-admission and unblocks the barrier."""
+        with self.registration_lock:
+            if wid in self.active_workers:
+                self.active_workers.discard(wid)
+                self._free_ids.append(wid)
+                self._free_ids.sort()
+                self.membership_epoch += 1
+        with self.sync_cv:
+            self.sync_cv.notify_all()
+
+    # metrics --------------------------------------------------------------
+    def server_metrics(self) -> dict:
+        total_time = time.time() - self.start_time
+        avg_update = float(np.mean(self.update_times)) if self.update_times else 0.0
+        extra = {}
+        if self.mode == "async" and self.gradient_staleness:
+            n = max(1, sum(self.staleness_hist.values()))
+            extra = {
+                "async_updates": self.async_updates,
+                "average_gradient_staleness": round(float(np.mean(list(self.gradient_staleness.values()))), 2),
+                "max_staleness_observed": max(self.gradient_staleness.values()),
+                "rejected_updates": self.rejected_updates,
+                "running_mean_staleness": round(self.staleness_sum / n, 4),
+                "running_max_staleness": self.staleness_max,
+                "staleness_histogram": {str(k): v for k, v in sorted(self.staleness_hist.items())},
+            }
+        return M.server_final_metrics(
+            mode=self.mode, total_workers=self.total_workers, total_time=total_time,
+            global_step=self.global_step, total_updates=self.total_updates,
+            gradients_processed=self.gradients_processed, avg_update_time=avg_update,
+            learning_rate=self.learning_rate,
+            extra={**extra, "barrier_timeouts": self.barrier_timeouts,
+                   "membership_epoch": self.membership_epoch, "config": self.cfg.to_dict()})
+
+    def _print_final_statistics(self) -> None:
+        self.final_metrics = self.server_metrics()
+        M.emit(self.final_metrics, self.cfg.metrics_dir, "server")
+
+    def state_dict_numpy(self) -> Dict[str, np.ndarray]:
+        with self.param_lock:
+            return {k: np.array(v, copy=True) for k, v in self.parameters.items()}
+
+    def _log(self, msg: str) -> None:
+        if self.verbose:
+            print(msg, flush=True)
+
+
+def build_server(cfg: Config, servicer: Optional[ParameterServerServicer] = None,
+                 bind: str = "[::]", verbose: bool = False):
+    """Create (server, servicer, bound_port) without blocking.  Port 0 picks a free port."""
+    servicer = servicer or ParameterServerServicer(cfg.mode, cfg.workers, cfg.lr, cfg.staleness_bound,
+                                                   config=cfg, verbose=verbose)
+    # a true barrier parks up to W handler threads; leave room for fetches/registrations
+    pool = futures.ThreadPoolExecutor(max_workers=max(20, 2 * cfg.workers + 8))
+    server = grpc.server(pool, options=proto.GRPC_OPTIONS)
+    proto.add_ParameterServerServicer_to_server(servicer, server)
+    port = server.add_insecure_port(f"{bind}:{cfg.port}")
+    return server, servicer, port
+
+
+def serve(mode: str = "sync", total_workers: int = 4, learning_rate: float = 0.1, port: int = 8000,
+          staleness_bound: int = 5, config: Optional[Config] = None) -> None:
+    """Blocking entry point with the reference's signature (server.py:370) + staleness_bound."""
+    cfg = (config or Config()).replace(mode=mode, workers=total_workers, lr=learning_rate, port=port,
+                                       staleness_bound=staleness_bound).validate()
+    server, servicer, port = build_server(cfg, verbose=True)
+    server.start()
+    print(f"--- Parameter Server listening on port {port} ---")
+    print(f"Mode: {cfg.mode.upper()}, Workers: {cfg.workers}, LR: {cfg.lr}, staleness bound: {cfg.staleness_bound}")
+    try:
+        server.wait_for_termination()
+    except KeyboardInterrupt:
+        print("Server shutting down...")
+        server.stop(0)
+        if not servicer._final_emitted:
+            servicer._print_final_statistics()
+
+
+def main(argv=None) -> int:
+    from ..config import parse_server_cli
+    try:
+        cfg = parse_server_cli(argv)
+    except ValueError as e:
+        print(f"Error: {e}")
+        return 1
+    serve(cfg.mode, cfg.workers, cfg.lr, cfg.port, cfg.staleness_bound, config=cfg)
+    return 0
+
+
+if __name__ == "__main__":
+    raise SystemExit(main())

@@ -1,0 +1,91 @@
+"""BASELINE config 1: ResNet-18 CIFAR-100-shape synthetic, 1 server + 2 workers over gRPC
+localhost on CPU (plumbing, no GPU).  Also async mode and the sync == large-batch-SGD property."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+from dps_b200.config import Config
+from dps_b200.models.resnet import build_model
+from dps_b200.rpc import servicer as S
+from dps_b200.rpc.client import DistributedWorker
+from dps_b200.utils import metrics as M
+
+
+def _run_job(cfg: Config, steps: int, tmp_path):
+    server, sv, port = S.build_server(cfg.replace(port=0), bind="127.0.0.1")
+    server.start()
+    workers, errs = [], []
+
+    def run(i):
+        try:
+            w = DistributedWorker(f"127.0.0.1:{port}", f"w{i}", config=cfg)
+            w.connect_to_server()
+            w.setup_model()
+            w.setup_data()
+            w.max_steps = steps
+            workers.append(w)
+            w.run_training(evaluate=True, eval_batches=1)
+        except Exception as e:  # pragma: no cover
+            errs.append(e)
+
+    ths = [threading.Thread(target=run, args=(i,)) for i in range(cfg.workers)]
+    [t.start() for t in ths]
+    [t.join(300) for t in ths]
+    server.stop(0)
+    assert not errs, errs
+    return sv, workers
+
+
+@pytest.mark.parametrize("mode", ["sync", "async"])
+def test_one_server_two_workers_grpc_cpu(mode, tmp_path):
+    torch.set_num_threads(2)
+    cfg = Config(mode=mode, workers=2, lr=0.05, batch_size=8, epochs=1, train_samples=64, test_samples=16,
+                 metrics_dir=str(tmp_path), barrier_timeout_s=120)
+    sv, workers = _run_job(cfg, steps=2, tmp_path=tmp_path)
+    assert len(workers) == 2 and sorted(w.worker_id for w in workers) == [0, 1]
+    assert {w.partition for w in workers} == {(0, 32), (32, 64)}          # disjoint contiguous (C15)
+    assert all(w.local_step_counter == 2 for w in workers)
+    assert sv.gradients_processed == 4
+    assert sv.global_step == (2 if mode == "sync" else 4 - sv.rejected_updates)
+    # metrics: one server record, two worker records, aggregate schema (C23/C24/C29)
+    res = M.collect_dir(str(tmp_path), f"{mode}_2workers", str(tmp_path / "out" / "res.json"))
+    assert res["server_metrics"]["type"] == "SERVER_FINAL_METRICS"
+    assert res["server_metrics"]["mode"] == mode
+    agg = res["worker_metrics_aggregated"]
+    assert agg["num_workers"] == 2 and agg["total_local_steps"] == 4
+    assert {"epoch", "max_time", "avg_time", "min_time"} <= set(agg["epoch_times_by_epoch"][0])
+    # parameters actually moved and stayed finite
+    init = {k: v.detach().numpy() for k, v in build_model(100, seed=cfg.seed).state_dict().items()}
+    cur = sv.state_dict_numpy()
+    assert set(cur) == set(init) and len(cur) == 122
+    assert not np.allclose(cur["fc.weight"], init["fc.weight"])
+    assert all(np.isfinite(v).all() for v in cur.values() if v.dtype == np.float32)
+    # BN running stats were maintained on the server (Q5 fix, default policy 'mean')
+    assert not np.allclose(cur["bn1.running_mean"], 0.0)
+
+
+def test_sync_step_equals_large_batch_sgd():
+    """SURVEY §4.5 (CPU form): one sync round over W workers == one SGD step on the mean gradient."""
+    torch.manual_seed(0)
+    W = 2
+    model = build_model(100, seed=1)
+    init = {k: v.detach().clone() for k, v in model.state_dict().items()}
+    xs = [torch.randn(4, 3, 32, 32) for _ in range(W)]
+    ys = [torch.randint(0, 100, (4,)) for _ in range(W)]
+    sv = S.ParameterServerServicer("sync", W, 0.1, config=Config(nonblocking_sync=True, compress="none"),
+                                   initial_state={k: v.numpy() for k, v in init.items()})
+    grads_sum = None
+    for w in range(W):
+        model.load_state_dict(init)
+        model.train()
+        model.zero_grad()
+        torch.nn.functional.cross_entropy(model(xs[w]), ys[w]).backward()
+        g = {n: p.grad.numpy().copy() for n, p in model.named_parameters()}
+        sv._handle_sync_gradients(w, g, 0)
+        grads_sum = g if grads_sum is None else {k: grads_sum[k] + g[k] for k in g}
+    for n, p in init.items():
+        if n in grads_sum:
+            expect = p.numpy() - 0.1 * (grads_sum[n] / W)
+            np.testing.assert_allclose(sv.parameters[n], expect, rtol=1e-6, atol=1e-7)
