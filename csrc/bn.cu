@@ -1,0 +1,196 @@
+// Fused BatchNorm(+residual)+ReLU forward and backward on NHWC bf16 activations.
+//
+// Replaces nn.BatchNorm2d + torch.relu + the residual `out += shortcut(x)` of the reference blocks
+// (reference: src/parameter_server/server.py:25-40,49,67-68) and their autograd backward.
+//
+// Forward: the per-channel batch sums (sum, sum of squares) arrive from the producing conv's epilogue
+// (conv_tc.cu), so the forward is ONE bandwidth-bound pass: normalise + affine (+ residual) (+ ReLU),
+// bf16 out, plus saved mean / rstd and the running-statistics update (momentum 0.1, unbiased variance,
+// num_batches_tracked) done by CTA 0.
+// Backward: two passes.  reduce: dz = dy * (y > 0); per-channel sum(dz), sum(dz * xhat) (registers ->
+// shared -> one global atomic per channel per CTA), writes dz.  apply: dx = gamma*rstd*(dz - mean(dz)
+// - xhat*mean(dz*xhat)), and CTA 0 accumulates dgamma / dbeta into the flat gradient arena.
+#include "common.cuh"
+#include "../include/dps_b200_compute.h"
+
+namespace dps {
+
+constexpr int kBnThreads = 256;
+constexpr int kMaxC = 512;
+
+struct V8 {
+  float v[8];
+};
+__device__ __forceinline__ V8 unpack8(uint4 u) {
+  V8 r;
+  float2 f;
+  f = unpack_bf16x2(u.x); r.v[0] = f.x; r.v[1] = f.y;
+  f = unpack_bf16x2(u.y); r.v[2] = f.x; r.v[3] = f.y;
+  f = unpack_bf16x2(u.z); r.v[4] = f.x; r.v[5] = f.y;
+  f = unpack_bf16x2(u.w); r.v[6] = f.x; r.v[7] = f.y;
+  return r;
+}
+__device__ __forceinline__ uint4 pack8(const V8& r) {
+  return make_uint4(pack_bf16x2(r.v[0], r.v[1]), pack_bf16x2(r.v[2], r.v[3]), pack_bf16x2(r.v[4], r.v[5]),
+                    pack_bf16x2(r.v[6], r.v[7]));
+}
+
+__global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
+    const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
+    const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
+    float* __restrict__ save_mean, float* __restrict__ save_rstd, float* __restrict__ running_mean,
+    float* __restrict__ running_var, long long* __restrict__ num_batches, long long P, int C, int relu,
+    int training, float eps, float momentum) {
+  __shared__ float s_scale[kMaxC], s_shift[kMaxC];
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    float mean, var;
+    if (training) {
+      mean = stats[c] / (float)P;
+      var = fmaxf(stats[C + c] / (float)P - mean * mean, 0.f);
+    } else {
+      mean = running_mean[c];
+      var = running_var[c];
+    }
+    const float rstd = rsqrtf(var + eps);
+    const float sc = gamma[c] * rstd;
+    s_scale[c] = sc;
+    s_shift[c] = beta[c] - mean * sc;
+    if (training && blockIdx.x == 0) {
+      save_mean[c] = mean;
+      save_rstd[c] = rstd;
+      const float unbiased = var * (float)P / (float)max(1LL, P - 1);
+      running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
+      running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
+      if (c == 0) *num_batches += 1;
+    }
+  }
+  __syncthreads();
+  const int cg = C / 8;
+  const long long nvec = P * cg;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(v % cg) * 8;
+    V8 a = unpack8(ld_nc_v4(x + v * 8));
+    V8 r = {};
+    if (residual != nullptr) r = unpack8(ld_nc_v4(residual + v * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      float o = a.v[i] * s_scale[c0 + i] + s_shift[c0 + i] + r.v[i];
+      a.v[i] = relu ? fmaxf(o, 0.f) : o;
+    }
+    st_v4(y + v * 8, pack8(a));
+  }
+}
+
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
+    const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
+    const float* __restrict__ mean, const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
+    float* __restrict__ sums, long long P, int C, int relu) {
+  __shared__ float s_sum[2 * kMaxC];
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_sum[c] = 0.f;
+  __syncthreads();
+  const int cg = C / 8;                               // channel groups; 256 % cg == 0
+  const int my_cg = threadIdx.x % cg;
+  const int rows_per_pass = blockDim.x / cg;
+  const int c0 = my_cg * 8;
+  float mu[8], rs[8], a_dz[8], a_dzx[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { mu[i] = mean[c0 + i]; rs[i] = rstd[c0 + i]; a_dz[i] = 0.f; a_dzx[i] = 0.f; }
+  for (long long row = (long long)blockIdx.x * rows_per_pass + threadIdx.x / cg; row < P;
+       row += (long long)gridDim.x * rows_per_pass) {
+    const long long off = row * C + c0;
+    V8 g = unpack8(ld_nc_v4(dy + off));
+    V8 xv = unpack8(ld_nc_v4(x + off));
+    if (relu) {
+      V8 yv = unpack8(ld_nc_v4(y + off));
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g.v[i] = yv.v[i] > 0.f ? g.v[i] : 0.f;
+      st_v4(dz + off, pack8(g));
+    }
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      a_dz[i] += g.v[i];
+      a_dzx[i] += g.v[i] * (xv.v[i] - mu[i]) * rs[i];
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    atomicAdd(&s_sum[c0 + i], a_dz[i]);
+    atomicAdd(&s_sum[C + c0 + i], a_dzx[i]);
+  }
+  __syncthreads();
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) atomicAdd(sums + c, s_sum[c]);
+}
+
+__global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
+    const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean,
+    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ sums,
+    __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, long long P, int C) {
+  __shared__ float s_a[kMaxC], s_b[kMaxC], s_c[kMaxC];   // dx = s_a*dz + s_b*x + s_c
+  const float invP = 1.f / (float)P;
+  for (int c = threadIdx.x; c < C; c += blockDim.x) {
+    const float sdz = sums[c], sdzx = sums[C + c];
+    const float gr = gamma[c] * rstd[c];
+    // dx = gr * (dz - sdz/P - xhat * sdzx/P),  xhat = (x - mean) * rstd
+    const float k = gr * rstd[c] * sdzx * invP;
+    s_a[c] = gr;
+    s_b[c] = -k;
+    s_c[c] = -gr * sdz * invP + k * mean[c];
+    if (blockIdx.x == 0) {
+      dgamma[c] += sdzx;
+      dbeta[c] += sdz;
+    }
+  }
+  __syncthreads();
+  const int cg = C / 8;
+  const long long nvec = P * cg;
+  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
+    const int c0 = (int)(v % cg) * 8;
+    V8 g = unpack8(ld_nc_v4(dz + v * 8));
+    V8 xv = unpack8(ld_nc_v4(x + v * 8));
+#pragma unroll
+    for (int i = 0; i < 8; ++i) g.v[i] = s_a[c0 + i] * g.v[i] + s_b[c0 + i] * xv.v[i] + s_c[c0 + i];
+    st_v4(dx + v * 8, pack8(g));
+  }
+}
+
+}  // namespace dps
+
+using namespace dps;
+
+static int bn_grid(long long nvec) {
+  long long want = (nvec + kBnThreads - 1) / kBnThreads;
+  long long cap = 148 * 8;
+  return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
+}
+
+DPS_API int dps_bn_forward(const void* x, const float* stats, const float* gamma, const float* beta,
+                           const void* residual, void* y, float* save_mean, float* save_rstd, float* running_mean,
+                           float* running_var, long long* num_batches, long long P, int C, int relu, int training,
+                           float eps, float momentum, void* stream) {
+  if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
+  bn_fwd_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)x, stats, gamma, beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, save_mean,
+      save_rstd, running_mean, running_var, num_batches, P, C, relu, training, eps, momentum);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// sums must be zero on entry ([2*C] fp32).  dz may alias dy.  When relu == 0, dz is not written and the
+// apply pass should be given dy.
+DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
+                            const float* gamma, void* dz, float* sums, void* dx, float* dgamma, float* dbeta,
+                            long long P, int C, int relu, void* stream) {
+  if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
+  const int rows_per_pass = kBnThreads / (C / 8);
+  long long want = (P + rows_per_pass - 1) / rows_per_pass;
+  const int g1 = (int)(want < 148 * 4 ? (want < 1 ? 1 : want) : 148 * 4);
+  bn_bwd_reduce_kernel<<<g1, kBnThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz,
+      sums, P, C, relu);
+  DPS_CHECK(cudaGetLastError());
+  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)(relu ? dz : dy), (const __nv_bfloat16*)x, mean, rstd, gamma, sums, (__nv_bfloat16*)dx,
+      dgamma, dbeta, P, C);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,704 @@
+// Implicit-GEMM convolutions on the 5th-gen tensor cores: tcgen05.mma with TMEM accumulators,
+// operands staged by TMA (cp.async.bulk.tensor) into 128-byte-swizzled shared memory.
+//
+// Replaces the reference's nn.Conv2d calls -- ATen/oneDNN on CPU, cuDNN in the single-process
+// baseline (reference: src/parameter_server/server.py:24,26,32,48 and autograd's backward of them).
+// Activations are NHWC bf16, weights K-R-S-C bf16, accumulation fp32.
+//
+// Two kernels cover all twenty convs of the CIFAR-style ResNet-18 in all three passes:
+//
+//  tapconv_kernel  (fprop and dgrad)   D[128 pixels, BLOCK_N channels] = sum over "taps" of A_tap * B_tap
+//      A_tap : a 128-pixel x 64-channel box of the input, fetched by ONE 5-D tiled TMA at the tap's
+//              spatial offset.  Padding is TMA out-of-bounds zero fill (coordinates may be negative), so
+//              there is no im2col buffer and no boundary code.  Stride-2 convs read a "parity view"
+//              tensor map (dims: [pw*C+c, w/2, ph, h/2, n]) so every tap is again a dense box.
+//      B_tap : the weight slice of that tap.  fprop reads W as [Cout][(r,s,ci)] K-major; dgrad reads
+//              the SAME tensor MN-major ([co rows][ci contiguous]) -- no transposed weight copy.
+//      stride-2 dgrad is decomposed into the 4 output-parity classes (1/2/2/4 taps), no zero-stuffing.
+//      epilogue: tcgen05.ld -> bf16 -> smem staging -> coalesced stores; optional fused residual-gradient
+//              add (`addend`), optional fused per-channel sum / sum-of-squares for the following BatchNorm.
+//
+//  wgrad_kernel    dW[co, tap, ci] += sum over pixels dY[pix, co] * X_tap[pix, ci]
+//      both operands are pixel-major in memory == MN-major UMMA operands straight from TMA boxes;
+//      up to 4 taps x 128 ci of fp32 accumulators live in TMEM (512 columns); split over pixel ranges
+//      across CTAs, reduced with coalesced fp32 red.global.add into the flat gradient arena.
+//
+// Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
+// warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).
+#include "common.cuh"
+#include "../include/dps_b200.h"
+#include "../include/dps_b200_compute.h"
+
+#include <mutex>
+#include <vector>
+
+namespace dps {
+
+constexpr int kStages = 3;
+constexpr int kTileM = 128;         // pixels per CTA tile == UMMA M
+constexpr int kKBlock = 64;         // reduction elements per pipeline stage (one 128-byte swizzle row)
+constexpr int kABytes = kTileM * kKBlock * 2;   // 16 KiB
+constexpr int kThreads = 192;
+
+struct Tap {
+  int16_t c_off;   // added to the A channel coordinate (parity view: pw*C)
+  int16_t db;      // A coordinate offset along w
+  int16_t ph;      // A coordinate along the parity dim
+  int16_t da;      // A coordinate offset along h
+  int32_t k_off;   // B column offset of this tap
+};
+
+struct ConvParams {
+  int BW, BH, BN;                 // pixel box of a tile (BW*BH*BN == 128)
+  int tiles_w, tiles_h;           // tiles along w and h (tiles along n = gridDim.x / (tiles_w*tiles_h))
+  int red_blocks;                 // 64-wide reduction blocks per tap
+  int ngroups;                    // parity groups (gridDim.z)
+  int ntaps[4];
+  Tap taps[4][9];
+  int oph[4], opw[4];             // output parity offsets per group
+  int os;                         // output pixel stride (1, or 2 for stride-2 dgrad)
+  int out_H, out_W, out_C;        // output tensor dims (pixels are written at (h*os+oph, w*os+opw))
+  __nv_bfloat16* out;
+  const __nv_bfloat16* addend;    // optional, same shape as out
+  float* stats;                   // optional [2*out_C]: per-channel sum, sum of squares
+};
+
+template <int BLOCK_N>
+struct ConvSmem {
+  static constexpr int kBBytes = BLOCK_N * kKBlock * 2;
+  static constexpr int kStageBytes = kABytes + kBBytes;
+  static constexpr int kPitch = BLOCK_N * 2 + 16;                 // staging row pitch (bank-conflict free)
+  static constexpr int kBarOff = kStages * kStageBytes;
+  static constexpr int kTotal = kBarOff + 128 + 1024;             // + barriers + alignment slack
+  static_assert(kTileM * kPitch <= kStages * kStageBytes, "staging must fit in the pipeline buffers");
+};
+
+template <int BLOCK_N, bool B_MN>
+__global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                           const __grid_constant__ CUtensorMap tmB,
+                                                           const __grid_constant__ ConvParams p) {
+  using S = ConvSmem<BLOCK_N>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty = full + kStages;
+  uint64_t* tmem_full = empty + kStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  const int grp = blockIdx.z;
+  const int ntaps = p.ntaps[grp];
+  const int nkb = ntaps * p.red_blocks;
+
+  // tile -> first pixel
+  int t = blockIdx.x;
+  const int tw = t % p.tiles_w; t /= p.tiles_w;
+  const int th = t % p.tiles_h; t /= p.tiles_h;
+  const int w0 = tw * p.BW, h0 = th * p.BH, n0 = t * p.BN;
+  const int c_out0 = blockIdx.y * BLOCK_N;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      mbar_init(tmem_full, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, BLOCK_N);        // BLOCK_N fp32 columns (64 or 128: power of two >= 32)
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================== TMA producer =====================
+    if (elect_one()) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % kStages, ph = (kb / kStages) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        const Tap tp = p.taps[grp][kb / p.red_blocks];
+        const int cb = kb % p.red_blocks;
+        uint8_t* a = smem + s * S::kStageBytes;
+        uint8_t* b = a + kABytes;
+        mbar_expect_tx(&full[s], S::kStageBytes);
+        tma_load_5d(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
+        if (!B_MN) {
+          tma_load_2d(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0);
+        } else {
+#pragma unroll
+          for (int j = 0; j < BLOCK_N / 64; ++j)
+            tma_load_2d(b + j * 8192, &tmB, &full[s], tp.k_off + c_out0 + j * 64, cb * kKBlock);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one thread) =====================
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(kTileM, BLOCK_N, 0, B_MN ? 1 : 0);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % kStages, ph = (kb / kStages) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(smem + s * S::kStageBytes);
+        const uint32_t b_addr = a_addr + kABytes;
+        const uint64_t adesc = make_smem_desc(a_addr, 16, 1024);
+        const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+        for (int k = 0; k < kKBlock / 16; ++k) {
+          // advance 16 reduction elements: K-major +32 B inside the swizzle row; MN-major +16 rows of 128 B
+          const uint64_t ad = adesc + (uint64_t)(k * 2);
+          const uint64_t bd = bdesc + (uint64_t)(B_MN ? k * 128 : k * 2);
+          umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);            // smem slot free once these MMAs have read it
+      }
+      umma_commit(tmem_full);              // accumulator complete
+    }
+  } else {
+    // ===================== epilogue (4 warps) =====================
+    const int q = warp & 3;                // TMEM lane quadrant this warp may access
+    const int row = q * 32 + lane_id();    // tile row == pixel index in the box
+    mbar_wait(tmem_full, 0);
+    tc_fence_after();
+    uint8_t* stage = smem;                 // pipeline buffers are idle now: reuse as staging
+#pragma unroll
+    for (int c = 0; c < BLOCK_N / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
+      tmem_ld_wait();
+      uint4* dst = reinterpret_cast<uint4*>(stage + row * S::kPitch + c * 64);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        dst[j] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
+                            pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
+                            pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
+                            pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7])));
+      }
+    }
+    tc_fence_before();
+    asm volatile("bar.sync 1, 128;" ::: "memory");      // epilogue warps only
+    const int et = threadIdx.x - 64;                      // 0..127
+
+    if (p.stats != nullptr) {
+      // fused BatchNorm statistics over the bf16 values that are actually stored
+      constexpr int kHalves = 128 / BLOCK_N;              // 2 for N=64, 1 for N=128
+      const int ch = et % BLOCK_N, half = et / BLOCK_N;
+      const int r0 = half * (kTileM / kHalves), r1 = r0 + kTileM / kHalves;
+      float s = 0.f, ss = 0.f;
+      for (int rr = r0; rr < r1; ++rr) {
+        const float v = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage + rr * S::kPitch + ch * 2));
+        s += v;
+        ss += v * v;
+      }
+      atomicAdd(p.stats + c_out0 + ch, s);
+      atomicAdd(p.stats + p.out_C + c_out0 + ch, ss);
+    }
+
+    constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
+    constexpr int kRowsPerPass = 128 / kChunks;
+    const int chunk = et % kChunks;
+    const int boxhw = p.BW * p.BH;
+    for (int rr = et / kChunks; rr < kTileM; rr += kRowsPerPass) {
+      const int n = n0 + rr / boxhw;
+      const int rem = rr % boxhw;
+      const int oh = (h0 + rem / p.BW) * p.os + p.oph[grp];
+      const int ow = (w0 + rem % p.BW) * p.os + p.opw[grp];
+      const size_t off = (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
+      uint4 v = *reinterpret_cast<const uint4*>(stage + rr * S::kPitch + chunk * 16);
+      if (p.addend != nullptr) {
+        const uint4 a = ld_v4(p.addend + off);
+        float2 x, y;
+        x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
+      }
+      st_v4(p.out + off, v);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, BLOCK_N);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// wgrad
+// ------------------------------------------------------------------------------------------
+struct WgradParams {
+  int BW, BH, BN;                 // pixel box of one reduction block (BW*BH*BN == 64)
+  int tiles_w, tiles_h, tiles_n;  // reduction blocks along w, h, n
+  int nsplit;                     // CTAs along the pixel range (gridDim.x)
+  int co_tiles;                   // ceil(Cout/128)
+  int ci_chunks;                  // Cin / NB
+  int co_alias;                   // 1 when Cout == 64: rows 64..127 alias rows 0..63 (LBO = 0)
+  int ntap_groups;
+  int ntaps[4];
+  Tap taps[4][9];                 // A(X) coordinate offsets + dW column offset (tap*Cin)
+  int Cout, dw_pitch;             // dW row pitch in floats (9*Cin, or 32 for the stem)
+  int valid_cols;                 // columns of the ci chunk that exist in dW (stem: 27)
+  float* dw;
+};
+
+template <int NB>
+struct WgradSmem {
+  static constexpr int kDyBytes = 64 * 128 * 2;                   // [64 pix][128 co] as two 64-wide atoms
+  static constexpr int kXBytes = 64 * NB * 2;                     // one tap: [64 pix][NB ci]
+  static constexpr int kMaxTaps = 512 / NB;                       // TMEM columns
+  static constexpr int kStageBytes = kDyBytes + kMaxTaps * kXBytes;
+  static constexpr int kWStages = (NB == 128) ? 2 : 2;
+  static constexpr int kBarOff = kWStages * kStageBytes;
+  static constexpr int kTotal = kBarOff + 128 + 1024;
+};
+
+template <int NB>
+__global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
+                                                         const __grid_constant__ CUtensorMap tmX,
+                                                         const __grid_constant__ WgradParams p) {
+  using S = WgradSmem<NB>;
+  constexpr int kWS = S::kWStages;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
+  uint64_t* empty = full + kWS;
+  uint64_t* tmem_full = empty + kWS;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  const int warp = threadIdx.x >> 5;
+  // blockIdx.y enumerates (co_tile, ci_chunk, tap_group)
+  int y = blockIdx.y;
+  const int tg = y % p.ntap_groups; y /= p.ntap_groups;
+  const int cic = y % p.ci_chunks;  y /= p.ci_chunks;
+  const int cot = y;
+  const int ntaps = p.ntaps[tg];
+  const int total_blocks = p.tiles_w * p.tiles_h * p.tiles_n;
+  const int per = (total_blocks + p.nsplit - 1) / p.nsplit;
+  const int kb0 = blockIdx.x * per;
+  const int kb1 = min(total_blocks, kb0 + per);
+  const int nkb = max(0, kb1 - kb0);
+  const uint32_t dy_atom_bytes = 64 * 128;                         // one [64 pix][64 co] atom
+  const uint32_t stage_tx = (p.co_alias ? dy_atom_bytes : 2 * dy_atom_bytes) + ntaps * S::kXBytes;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmDy);
+    tma_prefetch_desc(&tmX);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int s = 0; s < kWS; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      mbar_init(tmem_full, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 512);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % kWS, ph = (i / kWS) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        int t = kb0 + i;
+        const int tw = t % p.tiles_w; t /= p.tiles_w;
+        const int th = t % p.tiles_h; t /= p.tiles_h;
+        const int w0 = tw * p.BW, h0 = th * p.BH, n0 = t * p.BN;
+        uint8_t* dy = smem + s * S::kStageBytes;
+        uint8_t* x = dy + S::kDyBytes;
+        mbar_expect_tx(&full[s], stage_tx);
+        tma_load_5d(dy, &tmDy, &full[s], cot * 128, w0, 0, h0, n0);
+        if (!p.co_alias) tma_load_5d(dy + dy_atom_bytes, &tmDy, &full[s], cot * 128 + 64, w0, 0, h0, n0);
+        for (int tp = 0; tp < ntaps; ++tp) {
+          const Tap tap = p.taps[tg][tp];
+#pragma unroll
+          for (int j = 0; j < NB / 64; ++j)
+            tma_load_5d(x + tp * S::kXBytes + j * 8192, &tmX, &full[s], tap.c_off + cic * NB + j * 64,
+                        w0 + tap.db, tap.ph, h0 + tap.da, n0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(128, NB, 1, 1);       // both operands MN-major
+      for (int i = 0; i < nkb; ++i) {
+        const int s = i % kWS, ph = (i / kWS) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t dy_addr = smem_u32(smem + s * S::kStageBytes);
+        const uint32_t x_addr = dy_addr + S::kDyBytes;
+        const uint64_t adesc = make_smem_desc(dy_addr, p.co_alias ? 0 : dy_atom_bytes, 1024);
+        for (int tp = 0; tp < ntaps; ++tp) {
+          const uint64_t bdesc = make_smem_desc(x_addr + tp * S::kXBytes, 8192, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)          // 64 pixels = 4 x UMMA_K(16); +16 rows of 128 B per step
+            umma_bf16(tmem_base + tp * NB, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc,
+                      (i | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);
+      }
+      umma_commit(tmem_full);
+    }
+  } else {
+    const int q = warp & 3;
+    const int lane = lane_id();
+    const int et = threadIdx.x - 64;
+    float* stage = reinterpret_cast<float*>(smem);        // [128 co][33] fp32 transpose buffer (16.5 KiB)
+    if (nkb > 0) {
+      mbar_wait(tmem_full, 0);
+      tc_fence_after();
+      const int co_rows = p.co_alias ? 64 : min(128, p.Cout - cot * 128);
+      for (int tp = 0; tp < ntaps; ++tp) {
+        const int col_base = p.taps[tg][tp].k_off + cic * NB;          // dW column of this tap / ci chunk
+        for (int c = 0; c < NB / 32; ++c) {
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tp * NB + c * 32, r);
+          tmem_ld_wait();
+          const int row = q * 32 + lane;
+#pragma unroll
+          for (int j = 0; j < 32; ++j) stage[row * 33 + j] = __uint_as_float(r[j]);
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+          // coalesced reduction into dW: one warp instruction covers 32 consecutive ci of one co row
+          const int ci = c * 32 + lane;
+          if (ci < p.valid_cols - cic * NB) {
+            for (int rr = q; rr < co_rows; rr += 4)
+              atomicAdd(p.dw + (size_t)(cot * 128 + rr) * p.dw_pitch + col_base + ci, stage[rr * 33 + lane]);
+          }
+          asm volatile("bar.sync 1, 128;" ::: "memory");
+        }
+      }
+    }
+    (void)et;
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 512);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// host side: tensor maps + plans
+// ------------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static EncodeTiledFn get_encode() {
+  static EncodeTiledFn fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(p);
+  });
+  return fn;
+}
+
+// 5-D activation map over an NHWC bf16 tensor [N][H][W][C].
+//   parity == 0: dims (C, W, 1, H, N)
+//   parity == 1: dims (2C, W/2, 2, H/2, N)   (x[n, 2a+ph, 2b+pw, c] at coordinate (pw*C+c, b, ph, a, n))
+static int make_act_map(CUtensorMap* m, const void* base, int N, int H, int W, int C, int parity,
+                        int box_c, int bw, int bh, int bn) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) DPS_FAIL(3, "cuTensorMapEncodeTiled not available");
+  cuuint64_t dims[5], strides[4];
+  const cuuint64_t e = 2;
+  if (!parity) {
+    dims[0] = (cuuint64_t)C; dims[1] = W; dims[2] = 1; dims[3] = H; dims[4] = N;
+    strides[0] = (cuuint64_t)C * e;            // w
+    strides[1] = (cuuint64_t)W * C * e;        // (ph) -- size 1, value irrelevant but must be valid
+    strides[2] = (cuuint64_t)W * C * e;        // h
+    strides[3] = (cuuint64_t)H * W * C * e;    // n
+  } else {
+    dims[0] = (cuuint64_t)2 * C; dims[1] = W / 2; dims[2] = 2; dims[3] = H / 2; dims[4] = N;
+    strides[0] = (cuuint64_t)2 * C * e;        // b
+    strides[1] = (cuuint64_t)W * C * e;        // ph
+    strides[2] = (cuuint64_t)2 * W * C * e;    // a
+    strides[3] = (cuuint64_t)H * W * C * e;    // n
+  }
+  cuuint32_t box[5] = {(cuuint32_t)box_c, (cuuint32_t)bw, 1, (cuuint32_t)bh, (cuuint32_t)bn};
+  cuuint32_t es[5] = {1, 1, 1, 1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 5, const_cast<void*>(base), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) DPS_FAIL(4, "cuTensorMapEncodeTiled(act) failed: %d (N%d H%d W%d C%d par%d box %d,%d,%d,%d)",
+                                  (int)r, N, H, W, C, parity, box_c, bw, bh, bn);
+  return 0;
+}
+
+// 2-D weight map [rows][cols] bf16 with row pitch `pitch` elements.
+static int make_w_map(CUtensorMap* m, const void* base, int rows, int cols, int pitch, int box_cols, int box_rows) {
+  EncodeTiledFn enc = get_encode();
+  if (!enc) DPS_FAIL(3, "cuTensorMapEncodeTiled not available");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)pitch * 2};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t es[2] = {1, 1};
+  CUresult r = enc(m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(base), dims, strides, box, es,
+                   CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                   CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) DPS_FAIL(4, "cuTensorMapEncodeTiled(weight) failed: %d (rows %d cols %d pitch %d)", (int)r,
+                                  rows, cols, pitch);
+  return 0;
+}
+
+// choose a pixel box (bw, bh, bn) with bw*bh*bn == pixels, bw | W, bh | H, bn | N, preferring wide rows
+static bool pick_box(int pixels, int N, int H, int W, int* bw, int* bh, int* bn) {
+  for (int w = pixels; w >= 1; w >>= 1) {
+    if (w > W || W % w) continue;
+    for (int h = pixels / w; h >= 1; h >>= 1) {
+      if (h > H || H % h) continue;
+      const int n = pixels / (w * h);
+      if (w * h * n != pixels || n > N || N % n) continue;
+      *bw = w; *bh = h; *bn = n;
+      return true;
+    }
+  }
+  return false;
+}
+
+struct ConvPlan {
+  int kind;                       // 0 fprop, 1 dgrad, 2 wgrad
+  int block_n;
+  bool b_mn;
+  CUtensorMap tmA, tmB;
+  ConvParams cp;
+  WgradParams wp;
+  dim3 grid;
+  size_t smem;
+};
+
+template <int BN_, bool MN_>
+static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
+  auto kern = tapconv_kernel<BN_, MN_>;
+  static bool configured = false;
+  if (!configured) {
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<BN_>::kTotal));
+    configured = true;
+  }
+  kern<<<pl.grid, kThreads, ConvSmem<BN_>::kTotal, st>>>(pl.tmA, pl.tmB, pl.cp);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+template <int NB_>
+static int launch_wgrad(const ConvPlan& pl, cudaStream_t st) {
+  auto kern = wgrad_kernel<NB_>;
+  static bool configured = false;
+  if (!configured) {
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WgradSmem<NB_>::kTotal));
+    configured = true;
+  }
+  kern<<<pl.grid, kThreads, WgradSmem<NB_>::kTotal, st>>>(pl.tmA, pl.tmB, pl.wp);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+}  // namespace dps
+
+using namespace dps;
+
+// ------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------
+// fprop:  x [N][H][W][Cin] -> out [N][H/stride][W/stride][Cout];  w [Cout][R*R*Cin] (row pitch w_pitch)
+// dgrad:  x is dY [N][H/stride][W/stride][Cout] -> out dX [N][H][W][Cin] (H, W are ALWAYS the conv input dims)
+DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, const void* addend,
+                                 float* stats, int N, int H, int W, int Cin, int Cout, int R, int stride,
+                                 int w_cols, int w_pitch, void** out_plan) {
+  if (kind != 0 && kind != 1) DPS_FAIL(1, "kind must be 0 (fprop) or 1 (dgrad)");
+  if (R != 1 && R != 3) DPS_FAIL(1, "R must be 1 or 3");
+  if (stride != 1 && stride != 2) DPS_FAIL(1, "stride must be 1 or 2");
+  if (H % stride || W % stride) DPS_FAIL(1, "H, W must be divisible by stride");
+  const int pad = R / 2;
+  const int Ho = H / stride, Wo = W / stride;
+  const int red = (kind == 0) ? Cin : Cout;        // reduction channels
+  const int ngemm = (kind == 0) ? Cout : Cin;      // GEMM N
+  if (red % 64) DPS_FAIL(1, "reduction channels (%d) must be a multiple of 64", red);
+  if (ngemm % 64) DPS_FAIL(1, "output channels (%d) must be a multiple of 64", ngemm);
+  ConvPlan* pl = new ConvPlan();
+  memset(&pl->cp, 0, sizeof(pl->cp));
+  pl->kind = kind;
+  pl->block_n = (ngemm % 128 == 0) ? 128 : 64;
+  pl->b_mn = (kind == 1);
+  ConvParams& cp = pl->cp;
+  cp.red_blocks = red / 64;
+  // pixel tiles run over the conv OUTPUT grid for fprop, and over the dY-resolution grid for dgrad
+  // (stride 1: same as dX; stride 2: one tile of (a, b) per output-parity class)
+  const int TH = Ho, TW = Wo;
+  if (!pick_box(kTileM, N, TH, TW, &cp.BW, &cp.BH, &cp.BN)) {
+    delete pl;
+    DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
+  }
+  cp.tiles_w = TW / cp.BW;
+  cp.tiles_h = TH / cp.BH;
+  const int tiles_n = N / cp.BN;
+  cp.out = reinterpret_cast<__nv_bfloat16*>(out);
+  cp.addend = reinterpret_cast<const __nv_bfloat16*>(addend);
+  cp.stats = stats;
+  int rc = 0;
+  if (kind == 0) {
+    cp.out_H = Ho; cp.out_W = Wo; cp.out_C = Cout; cp.os = 1;
+    cp.ngroups = 1;
+    int nt = 0;
+    for (int r = 0; r < R; ++r)
+      for (int s = 0; s < R; ++s) {
+        Tap t;
+        if (stride == 1) {
+          t.c_off = 0; t.ph = 0; t.da = (int16_t)(r - pad); t.db = (int16_t)(s - pad);
+        } else {
+          // ih = 2*oh + r - pad  ->  parity ph = (r - pad) & 1, a = oh + floor((r - pad) / 2)
+          const int dr = r - pad, ds = s - pad;
+          const int ph = ((dr % 2) + 2) % 2, pw = ((ds % 2) + 2) % 2;
+          t.ph = (int16_t)ph; t.da = (int16_t)((dr - ph) / 2);
+          t.c_off = (int16_t)(pw * Cin); t.db = (int16_t)((ds - pw) / 2);
+        }
+        t.k_off = (r * R + s) * Cin;
+        cp.taps[0][nt++] = t;
+      }
+    cp.ntaps[0] = nt;
+    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW, cp.BH, cp.BN);
+    if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->block_n);
+  } else {
+    cp.out_H = H; cp.out_W = W; cp.out_C = Cin; cp.os = stride;
+    if (stride == 1) {
+      cp.ngroups = 1;
+      int nt = 0;
+      for (int r = 0; r < R; ++r)
+        for (int s = 0; s < R; ++s) {
+          Tap t;
+          t.c_off = 0; t.ph = 0; t.da = (int16_t)(pad - r); t.db = (int16_t)(pad - s);
+          t.k_off = (r * R + s) * Cin;
+          cp.taps[0][nt++] = t;
+        }
+      cp.ntaps[0] = nt;
+    } else {
+      // dX[n, 2a+ph, 2b+pw] = sum over (r, s) with (ph + pad - r), (pw + pad - s) even of
+      //                       dY[n, a + (ph+pad-r)/2, b + (pw+pad-s)/2] * W[:, r, s, :]
+      int g = 0;
+      for (int ph = 0; ph < 2; ++ph)
+        for (int pw = 0; pw < 2; ++pw) {
+          int nt = 0;
+          for (int r = 0; r < R; ++r)
+            for (int s = 0; s < R; ++s) {
+              const int dr = ph + pad - r, ds = pw + pad - s;
+              if ((dr & 1) || (ds & 1)) continue;
+              Tap t;
+              t.c_off = 0; t.ph = 0; t.da = (int16_t)(dr / 2); t.db = (int16_t)(ds / 2);
+              t.k_off = (r * R + s) * Cin;
+              cp.taps[g][nt++] = t;
+            }
+          if (nt == 0) continue;               // 1x1 stride-2: only parity (0,0) receives gradient
+          cp.ntaps[g] = nt; cp.oph[g] = ph; cp.opw[g] = pw;
+          ++g;
+        }
+      cp.ngroups = g;
+    }
+    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW, cp.BH, cp.BN);
+    if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, 64);
+  }
+  if (rc) { delete pl; return rc; }
+  pl->grid = dim3(cp.tiles_w * cp.tiles_h * tiles_n, ngemm / pl->block_n, cp.ngroups);
+  *out_plan = pl;
+  return 0;
+}
+
+// wgrad: dw[Cout][dw_pitch] (fp32, accumulated with atomics: caller zeroes) += dY^T * im2col(X)
+DPS_API int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout,
+                                  int R, int stride, int valid_cols, int dw_pitch, int nsplit, void** out_plan) {
+  if (R != 1 && R != 3) DPS_FAIL(1, "R must be 1 or 3");
+  if (Cin % 64 || Cout % 64) DPS_FAIL(1, "channels must be multiples of 64");
+  const int pad = R / 2;
+  const int Ho = H / stride, Wo = W / stride;
+  ConvPlan* pl = new ConvPlan();
+  memset(&pl->wp, 0, sizeof(pl->wp));
+  pl->kind = 2;
+  WgradParams& wp = pl->wp;
+  const int NB = (Cin % 128 == 0) ? 128 : 64;
+  pl->block_n = NB;
+  if (!pick_box(64, N, Ho, Wo, &wp.BW, &wp.BH, &wp.BN)) {
+    delete pl;
+    DPS_FAIL(1, "no 64-pixel box divides N=%d H=%d W=%d", N, Ho, Wo);
+  }
+  wp.tiles_w = Wo / wp.BW; wp.tiles_h = Ho / wp.BH; wp.tiles_n = N / wp.BN;
+  wp.co_alias = (Cout == 64);
+  wp.co_tiles = (Cout + 127) / 128;
+  if (!wp.co_alias && Cout % 128) { delete pl; DPS_FAIL(1, "Cout must be 64 or a multiple of 128"); }
+  wp.ci_chunks = Cin / NB;
+  wp.Cout = Cout; wp.dw_pitch = dw_pitch; wp.dw = dw;
+  wp.valid_cols = valid_cols;
+  const int max_taps = 512 / NB;
+  const int total_taps = R * R;
+  // balanced tap groups
+  const int ngroups = (total_taps + max_taps - 1) / max_taps;
+  wp.ntap_groups = ngroups;
+  int idx = 0;
+  for (int g = 0; g < ngroups; ++g) {
+    const int cnt = total_taps / ngroups + (g < total_taps % ngroups ? 1 : 0);
+    wp.ntaps[g] = cnt;
+    for (int i = 0; i < cnt; ++i, ++idx) {
+      const int r = idx / R, s = idx % R;
+      Tap t;
+      if (stride == 1) {
+        t.c_off = 0; t.ph = 0; t.da = (int16_t)(r - pad); t.db = (int16_t)(s - pad);
+      } else {
+        const int dr = r - pad, ds = s - pad;
+        const int ph = ((dr % 2) + 2) % 2, pw = ((ds % 2) + 2) % 2;
+        t.ph = (int16_t)ph; t.da = (int16_t)((dr - ph) / 2);
+        t.c_off = (int16_t)(pw * Cin); t.db = (int16_t)((ds - pw) / 2);
+      }
+      t.k_off = idx * Cin;
+      wp.taps[g][i] = t;
+    }
+  }
+  const int total_blocks = wp.tiles_w * wp.tiles_h * wp.tiles_n;
+  const int ny = wp.co_tiles * wp.ci_chunks * ngroups;
+  if (nsplit <= 0) nsplit = (148 + ny - 1) / ny;
+  if (nsplit > total_blocks) nsplit = total_blocks;
+  wp.nsplit = nsplit;
+  int rc = make_act_map(&pl->tmA, dy, N, Ho, Wo, Cout, 0, 64, wp.BW, wp.BH, wp.BN);
+  if (!rc) rc = make_act_map(&pl->tmB, x, N, H, W, Cin, stride == 2, 64, wp.BW, wp.BH, wp.BN);
+  if (rc) { delete pl; return rc; }
+  pl->grid = dim3(nsplit, ny, 1);
+  *out_plan = pl;
+  return 0;
+}
+
+DPS_API int dps_conv_plan_run(void* plan, void* stream) {
+  ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
+  cudaStream_t st = (cudaStream_t)stream;
+  if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
+  if (pl->b_mn) return pl->block_n == 128 ? launch_tapconv<128, true>(*pl, st) : launch_tapconv<64, true>(*pl, st);
+  return pl->block_n == 128 ? launch_tapconv<128, false>(*pl, st) : launch_tapconv<64, false>(*pl, st);
+}
+
+DPS_API int dps_conv_plan_destroy(void* plan) {
+  delete reinterpret_cast<ConvPlan*>(plan);
+  return 0;
+}
+
+DPS_API int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* smem_bytes) {
+  ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
+  grid_xyz[0] = pl->grid.x; grid_xyz[1] = pl->grid.y; grid_xyz[2] = pl->grid.z;
+  *block_n = pl->block_n;
+  *smem_bytes = pl->kind == 2 ? (pl->block_n == 128 ? WgradSmem<128>::kTotal : WgradSmem<64>::kTotal)
+                              : (pl->block_n == 128 ? ConvSmem<128>::kTotal : ConvSmem<64>::kTotal);
+  return 0;
+}

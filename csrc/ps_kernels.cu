@@ -1,0 +1,500 @@
+// Parameter-server data path on NVLink peer memory: Push (sync), Pull, Async enqueue / scan / apply.
+//
+// One process per GPU; every GPU is a worker AND the owner of one shard of the parameter store.
+// The flat parameter arena (forward-ordered, see store/shardmap.py) is sharded BLOCK-CYCLICALLY:
+// global block k (BS elements) lives on owner k % W at local block k / W, so a pull streams the
+// arena front-to-back from all owners at once.
+//
+// What each kernel replaces in the reference (src/parameter_server/server.py, src/workers/worker.py):
+//   push_sync   : compress_gradients (worker.py:264-268) + pickle/gRPC push (worker.py:289-301) +
+//                 decompress (server.py:232-237) + W-way mean (server.py:145-169) + SGD (server.py:126-143)
+//                 -> one kernel: fp32 grad -> fp16 tiles stored straight into the owner's staging slot
+//                 over NVLink, per-source arrival counters (release/acquire at system scope), then the
+//                 owner reduces in registers and updates its fp32 master shard (+momentum, +weight decay).
+//   pull_bcast  : pickle.dumps(params)/FetchParameters/load_state_dict (server.py:213-230, worker.py:233-262)
+//                 -> owner casts its updated shard to bf16 and stores it into every worker's weight arena.
+//   async_*     : the gRPC thread pool + param_lock + staleness logic (server.py:171-186, 290-304)
+//                 -> a device-side arrival ring per owner (ticketed slots), a per-shard version counter,
+//                 and a scan/apply pair that applies arrivals in ticket order with
+//                 weight = max(floor, 1/(1+alpha*staleness)) or rejects them (staleness > bound).
+//
+// No NCCL and no host round trip on this path.  All cross-GPU flags use st.release.sys / ld.acquire.sys.
+#include "common.cuh"
+#include "../include/dps_b200.h"
+
+thread_local char g_dps_err[512] = {0};
+
+namespace dps {
+
+constexpr int VEC = 8;  // elements per thread per iteration (16 B of fp16/bf16, 32 B of fp32)
+
+__device__ __forceinline__ long long global_index(long long l, int owner, int W, int BS) {
+  long long lb = l / BS;
+  return (lb * W + owner) * (long long)BS + (l - lb * BS);
+}
+
+struct F8 {
+  float v[8];
+};
+__device__ __forceinline__ F8 load_f32x8(const float* p) {
+  F8 r;
+  uint4 a = ld_v4(p), b = ld_v4(p + 4);
+  r.v[0] = __uint_as_float(a.x); r.v[1] = __uint_as_float(a.y); r.v[2] = __uint_as_float(a.z); r.v[3] = __uint_as_float(a.w);
+  r.v[4] = __uint_as_float(b.x); r.v[5] = __uint_as_float(b.y); r.v[6] = __uint_as_float(b.z); r.v[7] = __uint_as_float(b.w);
+  return r;
+}
+__device__ __forceinline__ void store_f32x8(float* p, const F8& r) {
+  st_v4(p, make_uint4(__float_as_uint(r.v[0]), __float_as_uint(r.v[1]), __float_as_uint(r.v[2]), __float_as_uint(r.v[3])));
+  st_v4(p + 4, make_uint4(__float_as_uint(r.v[4]), __float_as_uint(r.v[5]), __float_as_uint(r.v[6]), __float_as_uint(r.v[7])));
+}
+__device__ __forceinline__ uint4 to_f16x8(const F8& r) {
+  return make_uint4(pack_f16x2(r.v[0], r.v[1]), pack_f16x2(r.v[2], r.v[3]), pack_f16x2(r.v[4], r.v[5]),
+                    pack_f16x2(r.v[6], r.v[7]));
+}
+__device__ __forceinline__ uint4 to_bf16x8(const F8& r) {
+  return make_uint4(pack_bf16x2(r.v[0], r.v[1]), pack_bf16x2(r.v[2], r.v[3]), pack_bf16x2(r.v[4], r.v[5]),
+                    pack_bf16x2(r.v[6], r.v[7]));
+}
+__device__ __forceinline__ void acc_f16x8(F8& a, uint4 h, float w) {
+  float2 f;
+  f = unpack_f16x2(h.x); a.v[0] += w * f.x; a.v[1] += w * f.y;
+  f = unpack_f16x2(h.y); a.v[2] += w * f.x; a.v[3] += w * f.y;
+  f = unpack_f16x2(h.z); a.v[4] += w * f.x; a.v[5] += w * f.y;
+  f = unpack_f16x2(h.w); a.v[6] += w * f.x; a.v[7] += w * f.y;
+}
+
+// Spin until *flag >= target (acquire, system scope).  Returns false on timeout.
+__device__ __forceinline__ bool wait_ge(const uint32_t* flag, uint32_t target, unsigned long long timeout_ns) {
+  if ((int32_t)(ld_acquire_sys(flag) - target) >= 0) return true;
+  const uint64_t t0 = globaltimer_ns();
+  while ((int32_t)(ld_acquire_sys(flag) - target) < 0) {
+    __nanosleep(64);
+    if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) return false;
+  }
+  return true;
+}
+
+// ------------------------------------------------------------------------------------------
+// PUSH (sync): scatter fp16 gradient tiles to owners, barrier on per-source arrival counters,
+// W-way mean + SGD(momentum, weight decay) on the owner's fp32 master shard.
+// grid = G CTAs (G <= resident CTAs: owner-side CTAs spin, so the whole grid must be co-resident).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ DpsTables T, uint32_t step,
+                                                        float lr, float momentum, float weight_decay,
+                                                        int compress_fp16, unsigned long long timeout_ns) {
+  const int W = T.world, BS = T.block_elems;
+  const long long E = T.shard_elems;
+  const int G = gridDim.x, b = blockIdx.x;
+  const long long per = ((E / VEC + G - 1) / G) * VEC;       // elements per CTA per shard
+  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  __shared__ uint32_t s_present;
+
+  // ---- phase A: every rank handled by this launch sends its slice of every shard to that shard's owner
+  for (int r = T.rank_lo; r < T.rank_hi; ++r) {
+    float* grad = T.grad[r];
+    for (int oo = 0; oo < W; ++oo) {
+      const int o = (r + 1 + oo) % W;                        // rotate so owners are hit evenly
+      uint16_t* dst = T.stage[o] + (long long)r * E;           // peer-mapped staging slot [src=r]
+      for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+        const long long g = global_index(l, o, W, BS);
+        F8 v = load_f32x8(grad + g);
+        if (!compress_fp16) {                                 // fp32 wire: two fp16 planes is not lossless; keep
+          // uncompressed mode stores fp32 into a staging buffer twice as large (slot stride 2E halfs)
+          store_f32x8(reinterpret_cast<float*>(T.stage[o]) + (long long)r * E + l, v);
+        } else {
+          st_v4(dst + l, to_f16x8(v));
+        }
+        F8 z = {};                                            // gradients are consumed: zero for next step
+        store_f32x8(grad + g, z);
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        red_release_sys_add(T.flags[o] + DPS_F_ARRIVE + r, 1u);
+        if (b == 0) st_release_sys(T.flags[o] + DPS_F_HEARTBEAT + r, step + 1);
+      }
+    }
+  }
+
+  // ---- phase B: owners wait for all sources, reduce and update
+  const uint32_t target = (step + 1) * (uint32_t)G;
+  for (int o = T.rank_lo; o < T.rank_hi; ++o) {
+    if (threadIdx.x == 0) {
+      uint32_t present = 0;
+      for (int s = 0; s < W; ++s)
+        if (wait_ge(T.flags[o] + DPS_F_ARRIVE + s, target, timeout_ns)) present |= 1u << s;
+      if (present != (W >= 32 ? 0xffffffffu : ((1u << W) - 1u))) {
+        atomicOr(T.flags[o] + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
+        T.flags[o][DPS_F_MISSING] = ~present;
+      }
+      s_present = present;
+    }
+    __syncthreads();
+    const uint32_t present = s_present;
+    const float inv = 1.0f / (float)max(1, __popc(present));
+    float* master = T.master[o];
+    float* mom = T.mom[o];
+    for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+      F8 g = {};
+      for (int s = 0; s < W; ++s) {
+        if (!((present >> s) & 1u)) continue;
+        if (compress_fp16) {
+          acc_f16x8(g, ld_v4(T.stage[o] + (long long)s * E + l), 1.0f);
+        } else {
+          F8 t = load_f32x8(reinterpret_cast<const float*>(T.stage[o]) + (long long)s * E + l);
+#pragma unroll
+          for (int i = 0; i < 8; ++i) g.v[i] += t.v[i];
+        }
+      }
+      F8 p = load_f32x8(master + l);
+      if (momentum != 0.0f) {
+        F8 m = load_f32x8(mom + l);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float gi = g.v[i] * inv + weight_decay * p.v[i];
+          m.v[i] = momentum * m.v[i] + gi;
+          p.v[i] = p.v[i] - lr * m.v[i];
+        }
+        store_f32x8(mom + l, m);
+      } else {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float gi = g.v[i] * inv + weight_decay * p.v[i];
+          p.v[i] = p.v[i] - lr * gi;                        // == reference p - lr*g when wd == 0
+        }
+      }
+      store_f32x8(master + l, p);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0 && b == 0) T.flags[o][DPS_F_VERSION] = step + 1;
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// PULL: owner casts its fp32 shard to bf16 and stores it into every worker's weight arena
+// (plus an fp32 copy of the "small" head of the arena: BN affine parameters and fc bias).
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__ DpsTables T, uint32_t step) {
+  const int W = T.world, BS = T.block_elems;
+  const long long E = T.shard_elems, n_small = T.n_small;
+  const int G = gridDim.x, b = blockIdx.x;
+  const long long per = ((E / VEC + G - 1) / G) * VEC;
+  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  for (int o = T.rank_lo; o < T.rank_hi; ++o) {
+    const float* master = T.master[o];
+    for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+      const long long g = global_index(l, o, W, BS);
+      const F8 p = load_f32x8(master + l);
+      const uint4 h = to_bf16x8(p);
+      for (int ww = 0; ww < W; ++ww) {
+        const int w = (o + ww) % W;                          // start with the local copy, then peers
+        st_v4(T.wbf16[w] + g, h);
+        if (g < n_small) store_f32x8(T.small[w] + g, p);
+      }
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      for (int w = 0; w < W; ++w) red_release_sys_add(T.flags[w] + DPS_F_PULLCOUNT, 1u);
+    }
+  }
+}
+
+// Worker side of the pull: block the stream until all W owners have delivered `step`.
+__global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, uint32_t step, uint32_t ctas_per_owner,
+                                 unsigned long long timeout_ns) {
+  if (threadIdx.x == 0) {
+    const uint32_t target = (step + 1) * ctas_per_owner * (uint32_t)T.world;
+    if (!wait_ge(T.flags[rank] + DPS_F_PULLCOUNT, target, timeout_ns))
+      atomicOr(T.flags[rank] + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// ASYNC: arrival ring.  grid = (G, W): blockIdx.y selects the owner.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__ DpsTables T, int r, uint32_t step,
+                                                         unsigned long long timeout_ns) {
+  const int W = T.world, BS = T.block_elems, R = T.ring_slots;
+  const long long E = T.shard_elems;
+  const int G = gridDim.x, b = blockIdx.x;
+  const int o = (r + 1 + blockIdx.y) % W;
+  const long long per = ((E / VEC + G - 1) / G) * VEC;
+  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  uint32_t* lf = T.flags[r];                                  // my local flag block
+  uint32_t* of = T.flags[o];                                  // owner's flag block (peer)
+  __shared__ uint32_t s_ticket;
+  if (threadIdx.x == 0) {
+    uint32_t ticket;
+    if (b == 0) {
+      ticket = atom_add_acqrel_sys(of + DPS_F_RING_TAIL, 1u);
+      // back-pressure: slot (ticket % R) is free once the consumer's head has passed ticket - R
+      const uint64_t t0 = globaltimer_ns();
+      while ((int32_t)(ld_acquire_sys(of + DPS_F_RING_HEAD) + (uint32_t)R - ticket) <= 0) {
+        __nanosleep(128);
+        if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) {
+          atomicOr(lf + DPS_F_ERROR, DPS_ERR_RING_FULL);
+          break;
+        }
+      }
+      uint32_t* hdr = of + DPS_F_SLOTS + (ticket % R) * 4;
+      hdr[1] = (uint32_t)r;
+      hdr[2] = lf[DPS_F_SEEN + o];                            // version of shard o this worker last pulled
+      // publish the ticket to the other CTAs of this (rank, owner) pair
+      lf[DPS_F_TICKET + 2 * o + 1] = ticket;
+      __threadfence();
+      st_release_sys(lf + DPS_F_TICKET + 2 * o, step + 1);
+    } else {
+      while (ld_acquire_sys(lf + DPS_F_TICKET + 2 * o) != step + 1) __nanosleep(32);
+      ticket = lf[DPS_F_TICKET + 2 * o + 1];
+    }
+    s_ticket = ticket;
+  }
+  __syncthreads();
+  const uint32_t ticket = s_ticket;
+  const uint32_t slot = ticket % (uint32_t)R;
+  uint16_t* dst = T.ring[o] + (long long)slot * E;
+  float* grad = T.grad[r];
+  for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+    const long long g = global_index(l, o, W, BS);
+    F8 v = load_f32x8(grad + g);
+    st_v4(dst + l, to_f16x8(v));
+    F8 z = {};
+    store_f32x8(grad + g, z);
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence_system();
+    red_release_sys_add(of + DPS_F_SLOTS + slot * 4, 1u);     // slot.done += 1 (complete at (use+1)*G)
+    if (b == 0) st_release_sys(of + DPS_F_HEARTBEAT + r, step + 1);
+  }
+}
+
+// Owner: examine the ring in ticket order, decide accept/reject + weight for each complete arrival.
+__global__ void async_scan_kernel(const __grid_constant__ DpsTables T, int o, uint32_t producer_ctas, int bound,
+                                  float alpha, float floor_w, int max_batch) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  uint32_t* f = T.flags[o];
+  const uint32_t R = (uint32_t)T.ring_slots;
+  uint32_t h = f[DPS_F_RING_HEAD], v = f[DPS_F_VERSION];
+  int n = 0, n_apply = 0;
+  while (n < max_batch && n < DPS_MAX_PLAN) {
+    const uint32_t slot = h % R;
+    const uint32_t need = (h / R + 1) * producer_ctas;
+    if ((int32_t)(ld_acquire_sys(f + DPS_F_SLOTS + slot * 4) - need) < 0) break;
+    const uint32_t src = f[DPS_F_SLOTS + slot * 4 + 1];
+    const uint32_t seen = f[DPS_F_SLOTS + slot * 4 + 2];
+    const int s = (int)(v - seen);
+    float w = 0.0f;
+    if (s > bound) {
+      f[DPS_F_STAT_REJECTED] += 1;
+    } else {
+      w = fmaxf(floor_w, 1.0f / (1.0f + alpha * (float)s));
+      v += 1;
+      n_apply += 1;
+      f[DPS_F_STAT_ACCEPTED] += 1;
+    }
+    const int sc = max(0, s);
+    f[DPS_F_STAT_SUM] += (uint32_t)sc;
+    f[DPS_F_STAT_MAX] = max(f[DPS_F_STAT_MAX], (uint32_t)sc);
+    f[DPS_F_STAT_HIST + min(sc, DPS_HIST_BINS - 1)] += 1;
+    if (src < 32) f[DPS_F_STAT_LAST + src] = (uint32_t)sc;
+    f[DPS_F_PLAN + 3 + n] = slot;
+    reinterpret_cast<float*>(f)[DPS_F_PLAN + 3 + DPS_MAX_PLAN + n] = w;
+    ++n;
+    ++h;
+  }
+  f[DPS_F_PLAN + 0] = (uint32_t)n;
+  f[DPS_F_PLAN + 1] = v;
+  f[DPS_F_PLAN + 2] = h;
+  f[DPS_F_APPLY_DONE] = 0;
+  if (n_apply > 0) st_release_sys(f + DPS_F_PUBSEQ, f[DPS_F_PUBSEQ] | 1u);   // odd: shard being rewritten
+}
+
+// Owner: apply the planned arrivals sequentially per element (momentum order preserved), publish bf16.
+__global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant__ DpsTables T, int o, float lr,
+                                                          float momentum, float weight_decay) {
+  uint32_t* f = T.flags[o];
+  const int n = (int)f[DPS_F_PLAN + 0];
+  if (n == 0) return;
+  const int W = T.world, BS = T.block_elems;
+  const long long E = T.shard_elems, n_small = T.n_small;
+  const int G = gridDim.x, b = blockIdx.x;
+  const long long per = ((E / VEC + G - 1) / G) * VEC;
+  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  __shared__ uint32_t s_slot[DPS_MAX_PLAN];
+  __shared__ float s_w[DPS_MAX_PLAN];
+  if (threadIdx.x < n) {
+    s_slot[threadIdx.x] = f[DPS_F_PLAN + 3 + threadIdx.x];
+    s_w[threadIdx.x] = reinterpret_cast<float*>(f)[DPS_F_PLAN + 3 + DPS_MAX_PLAN + threadIdx.x];
+  }
+  __syncthreads();
+  bool any = false;
+  for (int k = 0; k < n; ++k) any |= (s_w[k] > 0.0f);
+  float* master = T.master[o];
+  float* mom = T.mom[o];
+  if (any) {
+    for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+      F8 p = load_f32x8(master + l);
+      F8 m = {};
+      if (momentum != 0.0f) m = load_f32x8(mom + l);
+      for (int k = 0; k < n; ++k) {
+        const float w = s_w[k];
+        if (w <= 0.0f) continue;
+        F8 g = {};
+        acc_f16x8(g, ld_v4(T.ring[o] + (long long)s_slot[k] * E + l), w);   // staleness-weighted gradient
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float gi = g.v[i] + weight_decay * p.v[i];
+          if (momentum != 0.0f) { m.v[i] = momentum * m.v[i] + gi; gi = m.v[i]; }
+          p.v[i] = p.v[i] - lr * gi;
+        }
+      }
+      store_f32x8(master + l, p);
+      if (momentum != 0.0f) store_f32x8(mom + l, m);
+      const long long g = global_index(l, o, W, BS);
+      st_v4(T.pub[o] + l, to_bf16x8(p));
+      if (g < n_small) store_f32x8(T.pubsmall[o] + g, p);
+    }
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    __threadfence();
+    const uint32_t done = atomicAdd(f + DPS_F_APPLY_DONE, 1u) + 1;
+    if (done == (uint32_t)G) {                                 // last CTA publishes
+      __threadfence();
+      f[DPS_F_VERSION] = f[DPS_F_PLAN + 1];
+      if (any) st_release_sys(f + DPS_F_PUBSEQ, (f[DPS_F_PUBSEQ] | 1u) + 1u);   // even: consistent again
+      st_release_sys(f + DPS_F_RING_HEAD, f[DPS_F_PLAN + 2]);  // frees the consumed slots
+      f[DPS_F_PLAN + 0] = 0;
+    }
+  }
+}
+
+// Worker: gather every owner's published bf16 shard (peer reads) under a per-chunk seq-lock and record
+// the version seen (the `local_step` of the next push, reference worker.py:245,299).  grid = (G, W).
+__global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__ DpsTables T, int r) {
+  const int W = T.world, BS = T.block_elems;
+  const long long E = T.shard_elems, n_small = T.n_small;
+  const int G = gridDim.x, b = blockIdx.x;
+  const int o = (r + blockIdx.y) % W;
+  const long long per = ((E / VEC + G - 1) / G) * VEC;
+  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  const uint32_t* of = T.flags[o];
+  __shared__ uint32_t s_seq, s_ok;
+  for (int attempt = 0; attempt < 4; ++attempt) {
+    if (threadIdx.x == 0) {
+      uint32_t s0 = ld_acquire_sys(of + DPS_F_PUBSEQ);
+      int spins = 0;
+      while ((s0 & 1u) && spins++ < (1 << 16)) { __nanosleep(64); s0 = ld_acquire_sys(of + DPS_F_PUBSEQ); }
+      s_seq = s0;
+      if (b == 0) T.flags[r][DPS_F_SEEN + o] = ld_acquire_sys(of + DPS_F_VERSION);
+    }
+    __syncthreads();
+    for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+      const long long g = global_index(l, o, W, BS);
+      st_v4(T.wbf16[r] + g, ld_v4(T.pub[o] + l));
+      if (g < n_small) store_f32x8(T.small[r] + g, load_f32x8(T.pubsmall[o] + g));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      s_ok = (ld_acquire_sys(of + DPS_F_PUBSEQ) == s_seq) ? 1u : 0u;
+      if (!s_ok && attempt == 3) atomicAdd(T.flags[r] + DPS_F_TORN_PULLS, 1u);
+    }
+    __syncthreads();
+    if (s_ok) break;
+  }
+}
+
+// Initial publish (and re-publish after a checkpoint load): master -> pub bf16 (+small fp32), no version bump.
+__global__ void __launch_bounds__(256) publish_kernel(const __grid_constant__ DpsTables T, int o) {
+  const int W = T.world, BS = T.block_elems;
+  const long long E = T.shard_elems, n_small = T.n_small;
+  for (long long l = ((long long)blockIdx.x * blockDim.x + threadIdx.x) * VEC; l < E;
+       l += (long long)gridDim.x * blockDim.x * VEC) {
+    const F8 p = load_f32x8(T.master[o] + l);
+    const long long g = global_index(l, o, W, BS);
+    st_v4(T.pub[o] + l, to_bf16x8(p));
+    if (g < n_small) store_f32x8(T.pubsmall[o] + g, p);
+  }
+}
+
+}  // namespace dps
+
+// ==========================================================================================
+// C ABI
+// ==========================================================================================
+using namespace dps;
+
+DPS_API const char* dps_last_error(void) { return g_dps_err; }
+
+static int check_tables(const DpsTables* T) {
+  if (!T) DPS_FAIL(1, "null tables");
+  if (T->world < 1 || T->world > DPS_MAX_RANKS) DPS_FAIL(1, "world %d out of range", T->world);
+  if (T->rank_lo < 0 || T->rank_hi > T->world || T->rank_lo >= T->rank_hi) DPS_FAIL(1, "bad rank range");
+  if (T->block_elems <= 0 || T->block_elems % 8 != 0) DPS_FAIL(1, "block_elems must be a positive multiple of 8");
+  if (T->shard_elems <= 0 || T->shard_elems % T->block_elems != 0) DPS_FAIL(1, "shard_elems must be a multiple of block_elems");
+  return 0;
+}
+
+DPS_API int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
+                          int compress_fp16, int ctas, unsigned long long timeout_ns, void* stream) {
+  if (int e = check_tables(T)) return e;
+  push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
+                                                          timeout_ns);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_pull_bcast(const DpsTables* T, unsigned step, int ctas, void* stream) {
+  if (int e = check_tables(T)) return e;
+  pull_bcast_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_per_owner,
+                          unsigned long long timeout_ns, void* stream) {
+  if (int e = check_tables(T)) return e;
+  wait_pull_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, rank, step, (uint32_t)ctas_per_owner, timeout_ns);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_push_async(const DpsTables* T, int rank, unsigned step, int ctas, unsigned long long timeout_ns,
+                           void* stream) {
+  if (int e = check_tables(T)) return e;
+  if (T->ring_slots < 1 || T->ring_slots > DPS_MAX_SLOTS) DPS_FAIL(1, "ring_slots out of range");
+  dim3 grid(ctas, T->world);
+  push_async_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*T, rank, step, timeout_ns);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_async_apply(const DpsTables* T, int owner, int producer_ctas, int staleness_bound, float alpha,
+                            float floor_w, int max_batch, float lr, float momentum, float weight_decay, int ctas,
+                            void* stream) {
+  if (int e = check_tables(T)) return e;
+  async_scan_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, owner, (uint32_t)producer_ctas, staleness_bound, alpha,
+                                                         floor_w, max_batch);
+  DPS_CHECK(cudaGetLastError());
+  async_apply_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, owner, lr, momentum, weight_decay);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_pull_async(const DpsTables* T, int rank, int ctas, void* stream) {
+  if (int e = check_tables(T)) return e;
+  dim3 grid(ctas, T->world);
+  pull_async_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*T, rank);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_publish(const DpsTables* T, int owner, void* stream) {
+  if (int e = check_tables(T)) return e;
+  publish_kernel<<<148, 256, 0, (cudaStream_t)stream>>>(*T, owner);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -1,0 +1,212 @@
+"""On-box sharded parameter server: the device-side ParameterServer + Worker transport.
+
+Each rank owns one shard of the store (fp32 master + momentum) and one worker replica
+(bf16 weight arena + fp32 gradient arena).  The three data-path operations are the
+hand-written sm_100a kernels of csrc/ps_kernels.cu:
+
+    push  (sync)  : dps_push_sync   -- compress + peer store + arrival + reduce + SGD
+    pull          : dps_pull_bcast  -- cast + broadcast into every worker's bf16 arena
+    async         : dps_push_async / dps_async_apply / dps_pull_async -- arrival ring, per-shard
+                    version counter, staleness weight/reject
+
+Reference semantics preserved (reference: src/parameter_server/server.py:126-186, 264-304):
+mean over workers then ``p -= lr*g`` in sync mode; ``staleness = version - version_seen``,
+reject above the bound, weight ``max(0.1, 1/(1+0.1 s))`` in async mode.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Dict, List, Optional
+
+import torch
+
+from ..config import Config
+from ..ops import _lib as L
+from ..store.shardmap import Layout
+from .fabric import ArenaSpec, Fabric
+
+
+def _default_ctas(shard_elems: int) -> int:
+    # every CTA must be co-resident (owner CTAs spin on arrival counters): stay <= 1 CTA / SM
+    want = max(8, shard_elems // (256 * 8 * 4))
+    return int(min(128, want))
+
+
+class DevicePS:
+    def __init__(self, layout: Layout, cfg: Config, rank: int, world: int, device_index: int,
+                 emulate: bool = False, group=None, timeout_s: Optional[float] = None):
+        self.layout, self.cfg, self.rank, self.world = layout, cfg, rank, world
+        self.emulate = emulate
+        self.device = torch.device("cuda", device_index)
+        self.E, self.total, self.n_small = layout.shard_elems, layout.total, layout.n_small
+        self.R = max(1, min(L.MAX_SLOTS, cfg.async_ring_slots * world))
+        self.compress = cfg.compress == "fp16"
+        self.is_async = cfg.mode == "async"
+        self.ctas = _default_ctas(self.E)
+        self.async_ctas = max(1, min(self.ctas, 128 // world))
+        self.timeout_ns = int((timeout_s if timeout_s is not None else cfg.barrier_timeout_s) * 1e9)
+
+        spec = ArenaSpec()
+        spec.add("flags", L.FLAG_WORDS * 4)
+        spec.add("stage", world * self.E * (2 if self.compress else 4))
+        spec.add("wbf16", self.total * 2)
+        spec.add("small", self.n_small * 4)
+        if self.is_async:
+            spec.add("ring", self.R * self.E * 2)
+            spec.add("pub", self.E * 2)
+            spec.add("pubsmall", self.n_small * 4)
+        self.fabric = Fabric(rank, world, device_index, spec, emulate=emulate, group=group)
+        self.lib = self.fabric.lib
+
+        # local-only buffers
+        self.local = list(self.fabric.local_ranks())
+        dev = self.device
+        self.grad: Dict[int, torch.Tensor] = {r: torch.zeros(self.total, dtype=torch.float32, device=dev)
+                                              for r in self.local}
+        self.master: Dict[int, torch.Tensor] = {r: torch.zeros(self.E, dtype=torch.float32, device=dev)
+                                                for r in self.local}
+        self.mom: Dict[int, torch.Tensor] = {r: torch.zeros(self.E, dtype=torch.float32, device=dev)
+                                             for r in self.local}
+        self.wbf16 = {r: self.fabric.tensor(r, "wbf16", torch.bfloat16) for r in self.local}
+        self.small = {r: self.fabric.tensor(r, "small", torch.float32) for r in self.local}
+        self.flags = {r: self.fabric.tensor(r, "flags", torch.int32) for r in self.local}
+
+        t = L.DpsTables()
+        t.world, t.block_elems, t.ring_slots = world, layout.block_elems, self.R
+        t.shard_elems, t.n_small = self.E, self.n_small
+        t.rank_lo, t.rank_hi = (0, world) if emulate else (rank, rank + 1)
+        for r in range(world):
+            t.stage[r] = self.fabric.ptr(r, "stage")
+            t.wbf16[r] = self.fabric.ptr(r, "wbf16")
+            t.small[r] = self.fabric.ptr(r, "small")
+            t.flags[r] = self.fabric.ptr(r, "flags")
+            if self.is_async:
+                t.ring[r] = self.fabric.ptr(r, "ring")
+                t.pub[r] = self.fabric.ptr(r, "pub")
+                t.pubsmall[r] = self.fabric.ptr(r, "pubsmall")
+        for r in self.local:
+            t.grad[r] = self.grad[r].data_ptr()
+            t.master[r] = self.master[r].data_ptr()
+            t.mom[r] = self.mom[r].data_ptr()
+        self.tables = t
+        self._tp = C.byref(self.tables)
+        self.step = 0                       # sync round / pull sequence number
+        self.async_steps = {r: 0 for r in self.local}
+        self.launches = 0
+
+    # ------------------------------------------------------------------ state
+    def load_master(self, flat_global: torch.Tensor) -> None:
+        """Scatter a full fp32 arena into the local shard(s) and publish initial weights."""
+        shards = self.layout.to_shards(flat_global.to(self.device, torch.float32))
+        for r in self.local:
+            self.master[r].copy_(shards[r])
+            self.mom[r].zero_()
+        # initial weights for the local worker replicas (the "pull before first step")
+        for r in self.local:
+            self.wbf16[r].copy_(flat_global.to(self.device).to(torch.bfloat16))
+            self.small[r].copy_(flat_global[: self.n_small].to(self.device, torch.float32))
+        if self.is_async:
+            for r in self.local:
+                L.check(self.lib.dps_publish(self._tp, r, L.stream_ptr()), "publish")
+        torch.cuda.synchronize(self.device)
+
+    def gather_master(self, group=None) -> torch.Tensor:
+        """Full fp32 arena assembled from all shards (checkpoint path; not on the hot path)."""
+        if self.emulate or self.world == 1:
+            shards = torch.stack([self.master[r] for r in range(self.world)])
+        else:
+            import torch.distributed as dist
+            parts = [torch.empty_like(self.master[self.rank]) for _ in range(self.world)]
+            dist.all_gather(parts, self.master[self.rank], group=group)
+            shards = torch.stack(parts)
+        return self.layout.from_shards(shards)
+
+    def gather_momentum(self, group=None) -> torch.Tensor:
+        if self.emulate or self.world == 1:
+            shards = torch.stack([self.mom[r] for r in range(self.world)])
+        else:
+            import torch.distributed as dist
+            parts = [torch.empty_like(self.mom[self.rank]) for _ in range(self.world)]
+            dist.all_gather(parts, self.mom[self.rank], group=group)
+            shards = torch.stack(parts)
+        return self.layout.from_shards(shards)
+
+    # ------------------------------------------------------------------ sync
+    def push_sync(self, lr: Optional[float] = None, stream=None) -> None:
+        cfg = self.cfg
+        L.check(self.lib.dps_push_sync(self._tp, self.step, lr if lr is not None else cfg.lr, cfg.momentum,
+                                       cfg.weight_decay, int(self.compress), self.ctas, self.timeout_ns,
+                                       L.stream_ptr(stream)), "push_sync")
+        self.launches += 1
+
+    def pull(self, stream=None, wait: bool = True) -> None:
+        L.check(self.lib.dps_pull_bcast(self._tp, self.step, self.ctas, L.stream_ptr(stream)), "pull_bcast")
+        self.launches += 1
+        if wait:
+            for r in self.local:
+                L.check(self.lib.dps_wait_pull(self._tp, r, self.step, self.ctas, self.timeout_ns,
+                                               L.stream_ptr(stream)), "wait_pull")
+                self.launches += 1
+
+    def sync_round(self, lr: Optional[float] = None, stream=None) -> None:
+        """push -> (barrier, reduce, SGD) -> pull -> wait; advances the round counter."""
+        self.push_sync(lr, stream)
+        self.pull(stream)
+        self.step += 1
+
+    # ------------------------------------------------------------------ async
+    def pull_async(self, rank: Optional[int] = None, stream=None) -> None:
+        r = self.rank if rank is None else rank
+        L.check(self.lib.dps_pull_async(self._tp, r, self.async_ctas, L.stream_ptr(stream)), "pull_async")
+        self.launches += 1
+
+    def push_async(self, rank: Optional[int] = None, stream=None) -> None:
+        r = self.rank if rank is None else rank
+        L.check(self.lib.dps_push_async(self._tp, r, self.async_steps[r], self.async_ctas, self.timeout_ns,
+                                        L.stream_ptr(stream)), "push_async")
+        self.async_steps[r] += 1
+        self.launches += 1
+
+    def serve_async(self, owner: Optional[int] = None, lr: Optional[float] = None, stream=None,
+                    max_batch: int = L.MAX_PLAN) -> None:
+        """Owner role: drain the arrival ring (non-blocking) and apply in ticket order."""
+        o = self.rank if owner is None else owner
+        cfg = self.cfg
+        L.check(self.lib.dps_async_apply(self._tp, o, self.async_ctas, cfg.staleness_bound, cfg.staleness_alpha,
+                                         cfg.staleness_floor, max_batch, lr if lr is not None else cfg.lr,
+                                         cfg.momentum, cfg.weight_decay, self.ctas, L.stream_ptr(stream)),
+                "async_apply")
+        self.launches += 2
+
+    # ------------------------------------------------------------------ introspection
+    def flag_words(self, rank: Optional[int] = None) -> torch.Tensor:
+        return self.flags[self.rank if rank is None else rank].cpu()
+
+    def error_bits(self, rank: Optional[int] = None) -> int:
+        return int(self.flag_words(rank)[L.F_ERROR]) & 0xFFFFFFFF
+
+    def version(self, rank: Optional[int] = None) -> int:
+        return int(self.flag_words(rank)[L.F_VERSION])
+
+    def async_stats(self, rank: Optional[int] = None) -> dict:
+        f = self.flag_words(rank).tolist()
+        acc, rej = f[L.F_STAT_ACCEPTED], f[L.F_STAT_REJECTED]
+        n = max(1, acc + rej)
+        return {
+            "async_updates": acc, "rejected_updates": rej,
+            "running_mean_staleness": f[L.F_STAT_SUM] / n, "running_max_staleness": f[L.F_STAT_MAX],
+            "staleness_histogram": {str(i): f[L.F_STAT_HIST + i] for i in range(L.HIST_BINS) if f[L.F_STAT_HIST + i]},
+            "last_staleness_per_worker": f[L.F_STAT_LAST:L.F_STAT_LAST + self.world],
+            "version": f[L.F_VERSION], "torn_pulls": f[L.F_TORN_PULLS],
+            "heartbeat": f[L.F_HEARTBEAT:L.F_HEARTBEAT + self.world],
+        }
+
+    def bytes_per_push(self) -> int:
+        """Bytes this rank sends over NVLink per push (its slices of the other W-1 shards)."""
+        return (self.world - 1) * self.E * (2 if self.compress else 4)
+
+    def bytes_per_pull(self) -> int:
+        return (self.world - 1) * self.E * 2
+
+    def close(self) -> None:
+        self.fabric.close()

@@ -1,0 +1,122 @@
+"""every conv shape of the model x {fprop, dgrad, wgrad} against a plain PyTorch fp32
+reference of the same op (same bf16-rounded inputs)."""
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+
+# (H, Cin, Cout, R, stride)  -- CIFAR ResNet-18 conv shapes, H == W
+SHAPES = [
+    (32, 64, 64, 3, 1),      # layer1 (x4) and the im2col'ed stem GEMM shape family
+    (32, 64, 128, 3, 2),     # layer2.0.conv1
+    (16, 128, 128, 3, 1),    # layer2
+    (32, 64, 128, 1, 2),     # layer2 shortcut
+    (16, 128, 256, 3, 2),
+    (8, 256, 256, 3, 1),
+    (16, 128, 256, 1, 2),
+    (8, 256, 512, 3, 2),
+    (4, 512, 512, 3, 1),
+    (8, 256, 512, 1, 2),
+]
+N = 8
+
+
+def _mk(H, Cin, Cout, R, stride, seed=0):
+    g = torch.Generator(device="cuda").manual_seed(seed)
+    x = torch.randn(N, H, H, Cin, device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.randn(Cout, R, R, Cin, device="cuda", generator=g) / (R * R * Cin) ** 0.5).to(torch.bfloat16)
+    Ho = H // stride
+    dy = torch.randn(N, Ho, Ho, Cout, device="cuda", generator=g).to(torch.bfloat16)
+    return x, w, dy
+
+
+def _ref(x, w, dy, R, stride):
+    xf = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    wf = w.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    torch.backends.cudnn.allow_tf32 = False
+    torch.backends.cuda.matmul.allow_tf32 = False
+    y = F.conv2d(xf, wf, stride=stride, padding=R // 2)
+    y.backward(dy.float().permute(0, 3, 1, 2))
+    return (y.detach().permute(0, 2, 3, 1), xf.grad.permute(0, 2, 3, 1), wf.grad.permute(0, 2, 3, 1))
+
+
+def _relerr(a, b):
+    return float((a.float() - b.float()).abs().max() / (b.float().abs().max() + 1e-6))
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_fprop(shape):
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    x, w, dy = _mk(*shape)
+    y_ref, _, _ = _ref(x, w, dy, R, stride)
+    out = torch.zeros(N, H // stride, H // stride, Cout, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2 * Cout, device="cuda")
+    ConvPlan.fprop(x, w, out, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride, stats=stats).run()
+    torch.cuda.synchronize()
+    assert _relerr(out, y_ref) < 1.5e-2, _relerr(out, y_ref)
+    # fused BN statistics are taken over the stored bf16 values
+    of = out.float().reshape(-1, Cout)
+    assert torch.allclose(stats[:Cout], of.sum(0), rtol=2e-3, atol=2e-1)
+    assert torch.allclose(stats[Cout:], (of * of).sum(0), rtol=2e-3, atol=2e-1)
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_dgrad(shape):
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    x, w, dy = _mk(*shape)
+    _, dx_ref, _ = _ref(x, w, dy, R, stride)
+    if R == 1 and stride == 2:
+        # shortcut dgrad accumulates into an existing gradient at parity (0,0) and leaves the rest alone
+        base = torch.randn(N, H, H, Cin, device="cuda").to(torch.bfloat16)
+        dx = base.clone()
+        ConvPlan.dgrad(dy, w, dx, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride, addend=dx).run()
+        torch.cuda.synchronize()
+        want = base.float() + dx_ref
+        assert _relerr(dx, want) < 2e-2
+        assert torch.equal(dx[:, 1::2], base[:, 1::2]) and torch.equal(dx[:, :, 1::2], base[:, :, 1::2])
+    else:
+        dx = torch.full((N, H, H, Cin), 7.0, device="cuda", dtype=torch.bfloat16)
+        ConvPlan.dgrad(dy, w, dx, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride).run()
+        torch.cuda.synchronize()
+        assert _relerr(dx, dx_ref) < 1.5e-2, _relerr(dx, dx_ref)
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_wgrad(shape):
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    x, w, dy = _mk(*shape)
+    _, _, dw_ref = _ref(x, w, dy, R, stride)
+    dw = torch.zeros(Cout, R, R, Cin, device="cuda")
+    ConvPlan.wgrad(x, dy, dw, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride).run()
+    torch.cuda.synchronize()
+    assert _relerr(dw, dw_ref) < 5e-3, _relerr(dw, dw_ref)
+
+
+def test_dgrad_residual_addend_fused():
+    from dps_b200.ops.conv import ConvPlan
+    shape = (16, 128, 128, 3, 1)
+    H, Cin, Cout, R, stride = shape
+    x, w, dy = _mk(*shape)
+    _, dx_ref, _ = _ref(x, w, dy, R, stride)
+    res = torch.randn(N, H, H, Cin, device="cuda").to(torch.bfloat16)
+    dx = torch.zeros_like(res)
+    ConvPlan.dgrad(dy, w, dx, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride, addend=res).run()
+    torch.cuda.synchronize()
+    assert _relerr(dx, dx_ref + res.float()) < 2e-2
+
+
+def test_full_batch_layer1_shape():
+    from dps_b200.ops.conv import ConvPlan
+    Nb, H, C = 128, 32, 64
+    g = torch.Generator(device="cuda").manual_seed(1)
+    x = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.randn(C, 3, 3, C, device="cuda", generator=g) / 24).to(torch.bfloat16)
+    out = torch.empty(Nb, H, H, C, device="cuda", dtype=torch.bfloat16)
+    ConvPlan.fprop(x, w, out, N=Nb, H=H, W=H, Cin=C, Cout=C, R=3, stride=1).run()
+    ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
+    torch.cuda.synchronize()
+    assert _relerr(out, ref) < 1.5e-2
