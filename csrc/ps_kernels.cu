@@ -79,9 +79,11 @@ __device__ __forceinline__ bool wait_ge(const uint32_t* flag, uint32_t target, u
 // W-way mean + SGD(momentum, weight decay) on the owner's fp32 master shard.
 // grid = G CTAs (G <= resident CTAs: owner-side CTAs spin, so the whole grid must be co-resident).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ DpsTables T, uint32_t step,
-                                                        float lr, float momentum, float weight_decay,
+__global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ DpsTables T, uint32_t step_arg,
+                                                        float lr_arg, float momentum, float weight_decay,
                                                         int compress_fp16, unsigned long long timeout_ns) {
+  const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
+  const float lr = T.lr_ptr ? *T.lr_ptr : lr_arg;
   const int W = T.world, BS = T.block_elems;
   const long long E = T.shard_elems;
   const int G = gridDim.x, b = blockIdx.x;
@@ -174,7 +176,9 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
 // PULL: owner casts its fp32 shard to bf16 and stores it into every worker's weight arena
 // (plus an fp32 copy of the "small" head of the arena: BN affine parameters and fc bias).
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__ DpsTables T, uint32_t step) {
+__global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__ DpsTables T, uint32_t step_arg) {
+  const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
+  (void)step;
   const int W = T.world, BS = T.block_elems;
   const long long E = T.shard_elems, n_small = T.n_small;
   const int G = gridDim.x, b = blockIdx.x;
@@ -201,20 +205,23 @@ __global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__
 }
 
 // Worker side of the pull: block the stream until all W owners have delivered `step`.
-__global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, uint32_t step, uint32_t ctas_per_owner,
-                                 unsigned long long timeout_ns) {
+__global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, uint32_t step_arg,
+                                 uint32_t ctas_per_owner, unsigned long long timeout_ns, int bump) {
   if (threadIdx.x == 0) {
+    const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
     const uint32_t target = (step + 1) * ctas_per_owner * (uint32_t)T.world;
     if (!wait_ge(T.flags[rank] + DPS_F_PULLCOUNT, target, timeout_ns))
       atomicOr(T.flags[rank] + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
+    if (bump && T.step_ctr) T.step_ctr[0] = step + 1;     // last kernel of the round: safe to advance
   }
 }
 
 // ------------------------------------------------------------------------------------------
 // ASYNC: arrival ring.  grid = (G, W): blockIdx.y selects the owner.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__ DpsTables T, int r, uint32_t step,
-                                                         unsigned long long timeout_ns) {
+__global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__ DpsTables T, int r,
+                                                         uint32_t step_arg, unsigned long long timeout_ns) {
+  const uint32_t step = T.step_ctr ? T.step_ctr[1] : step_arg;
   const int W = T.world, BS = T.block_elems, R = T.ring_slots;
   const long long E = T.shard_elems;
   const int G = gridDim.x, b = blockIdx.x;
@@ -276,6 +283,7 @@ __global__ void async_scan_kernel(const __grid_constant__ DpsTables T, int o, ui
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   uint32_t* f = T.flags[o];
   const uint32_t R = (uint32_t)T.ring_slots;
+  if (T.step_ctr) T.step_ctr[1] += 1;                     // this rank's push (same stream, before) is done
   uint32_t h = f[DPS_F_RING_HEAD], v = f[DPS_F_VERSION];
   int n = 0, n_apply = 0;
   while (n < max_batch && n < DPS_MAX_PLAN) {
@@ -312,8 +320,9 @@ __global__ void async_scan_kernel(const __grid_constant__ DpsTables T, int o, ui
 }
 
 // Owner: apply the planned arrivals sequentially per element (momentum order preserved), publish bf16.
-__global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant__ DpsTables T, int o, float lr,
+__global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant__ DpsTables T, int o, float lr_arg,
                                                           float momentum, float weight_decay) {
+  const float lr = T.lr_ptr ? *T.lr_ptr : lr_arg;
   uint32_t* f = T.flags[o];
   const int n = (int)f[DPS_F_PLAN + 0];
   if (n == 0) return;
@@ -455,9 +464,9 @@ DPS_API int dps_pull_bcast(const DpsTables* T, unsigned step, int ctas, void* st
 }
 
 DPS_API int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_per_owner,
-                          unsigned long long timeout_ns, void* stream) {
+                          unsigned long long timeout_ns, int bump, void* stream) {
   if (int e = check_tables(T)) return e;
-  wait_pull_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, rank, step, (uint32_t)ctas_per_owner, timeout_ns);
+  wait_pull_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, rank, step, (uint32_t)ctas_per_owner, timeout_ns, bump);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

@@ -1,0 +1,360 @@
+"""Public on-box API: ``Job`` -> ``ParameterServer`` shard + ``Worker`` on every GPU.
+
+One process per GPU (``torchrun`` / ``dps_b200.launch``); rank == worker id == shard id.
+The roles keep the reference's names and responsibilities (reference:
+src/parameter_server/server.py:81 ParameterServerServicer, src/workers/worker.py:78 DistributedWorker)
+but the transport between them is the sm_100a Push / Pull / Async kernels over NVLink peer
+memory instead of pickle-over-gRPC; ``torch.distributed`` is used for bootstrap and for
+checkpoint gathers only.
+
+    job = Job(Config(mode="sync", workers=W, batch_size=128))
+    for x, y in loader:                       # pinned host tensors
+        loss = job.worker.train_step(x, y)    # H2D -> fwd/bwd -> push -> reduce+SGD -> pull, one graph replay
+    job.server.save_checkpoint("ckpt.pt")     # loads into the reference ResNet18 (strict=True)
+"""
+from __future__ import annotations
+
+import os
+import time
+from typing import Dict, Iterable, List, Optional, Tuple
+
+import torch
+
+from .config import Config
+from .models.resnet import build_model
+from .store.shardmap import Layout, build_layout
+from .utils import checkpoint as CK
+from .utils import metrics as M
+
+
+def _env_int(name: str, default: int) -> int:
+    try:
+        return int(os.environ.get(name, default))
+    except ValueError:
+        return default
+
+
+class Job:
+    """Bootstraps one rank: process group, symmetric arenas, parameter shard, worker engine."""
+
+    def __init__(self, cfg: Config, rank: Optional[int] = None, world: Optional[int] = None,
+                 device_index: Optional[int] = None, init_state: Optional[Dict[str, torch.Tensor]] = None):
+        from .parallel.ps_device import DevicePS
+        self.rank = _env_int("RANK", 0) if rank is None else rank
+        self.world = _env_int("WORLD_SIZE", 1) if world is None else world
+        self.device_index = _env_int("LOCAL_RANK", self.rank) if device_index is None else device_index
+        self.cfg = cfg.replace(workers=self.world).validate()
+        torch.cuda.set_device(self.device_index)
+        self.device = torch.device("cuda", self.device_index)
+        self.group = None
+        if self.world > 1:
+            import torch.distributed as dist
+            if not dist.is_initialized():
+                os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+                os.environ.setdefault("MASTER_PORT", "29500")
+                dist.init_process_group("nccl", rank=self.rank, world_size=self.world,
+                                        device_id=self.device)
+        model = build_model(self.cfg.num_classes, seed=self.cfg.seed)     # same seed on every rank (Q13)
+        if init_state is not None:
+            model.load_state_dict(init_state)
+        elif self.cfg.resume:
+            sd, side = CK.load(self.cfg.resume)
+            model.load_state_dict(sd)
+        self.model_cpu = model
+        self.layout: Layout = build_layout(model, self.world)
+        self.ps = DevicePS(self.layout, self.cfg, self.rank, self.world, self.device_index, group=self.group)
+        flat = torch.zeros(self.layout.total)
+        self.layout.flatten_into(flat, dict(model.named_parameters()))
+        self.ps.load_master(flat)
+        self.server = ParameterServer(self)
+        self.worker = Worker(self)
+        if self.cfg.resume:
+            _, side = CK.load(self.cfg.resume)
+            self.server.restore_sidecar(side)
+        self.barrier()
+
+    def barrier(self) -> None:
+        torch.cuda.synchronize(self.device)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.barrier(device_ids=[self.device_index])
+
+    def close(self) -> None:
+        self.barrier()
+        self.ps.close()
+
+
+class ParameterServer:
+    """This rank's shard of the store: fp32 master + momentum + version counter."""
+
+    def __init__(self, job: Job):
+        self.job, self.ps, self.cfg = job, job.ps, job.cfg
+        self.start_time = time.time()
+        self._final: Optional[dict] = None
+
+    @property
+    def global_step(self) -> int:
+        return self.ps.version()
+
+    def parameters(self) -> Dict[str, torch.Tensor]:
+        """Full fp32 parameters, state_dict-shaped (collective when world > 1)."""
+        flat = self.ps.gather_master(self.job.group)
+        return {k: v.cpu() for k, v in self.job.layout.unflatten(flat).items()}
+
+    def state_dict(self) -> Dict[str, torch.Tensor]:
+        """All 122 reference keys: trainable tensors from the shards + BN buffers per policy (Q5)."""
+        params = self.parameters()
+        bufs = self.job.worker.bn_buffers_for_checkpoint()
+        sd = {}
+        for k, v in self.job.model_cpu.state_dict().items():
+            sd[k] = params[k] if k in params else bufs.get(k, v.detach().clone())
+        return sd
+
+    def save_checkpoint(self, path: str) -> None:
+        sd = self.state_dict()
+        mom_flat = self.ps.gather_momentum(self.job.group)
+        mom = {k: v.cpu() for k, v in self.job.layout.unflatten(mom_flat).items()}
+        versions = self._all_versions()
+        if self.job.rank == 0:
+            CK.save(path, sd, global_step=max(versions), momentum=mom, shard_versions=versions,
+                    config=self.cfg.to_dict())
+        self.job.barrier()
+
+    def restore_sidecar(self, side: dict) -> None:
+        mom = side.get("momentum") or {}
+        if mom:
+            flat = torch.zeros(self.job.layout.total)
+            self.job.layout.flatten_into(flat, mom)
+            shards = self.job.layout.to_shards(flat.to(self.job.device))
+            self.ps.mom[self.job.rank].copy_(shards[self.job.rank])
+        step = int(side.get("global_step", 0))
+        self.ps.flags[self.job.rank][98] = step             # DPS_F_VERSION
+        if self.cfg.mode == "async":
+            # published shard carries the restored weights already (load_master); align the version view
+            pass
+
+    def _all_versions(self) -> List[int]:
+        v = torch.tensor([self.ps.version()], device=self.job.device, dtype=torch.int64)
+        if self.job.world == 1:
+            return [int(v)]
+        import torch.distributed as dist
+        out = [torch.zeros_like(v) for _ in range(self.job.world)]
+        dist.all_gather(out, v)
+        return [int(x) for x in out]
+
+    def metrics(self) -> dict:
+        total = time.time() - self.start_time
+        steps = self.global_step
+        extra = {"shard": self.job.rank, "shards": self.job.world, "transport": "nvlink-p2p",
+                 "error_bits": self.ps.error_bits(), "config": self.cfg.to_dict()}
+        if self.cfg.mode == "async":
+            st = self.ps.async_stats()
+            last = [s for s in st["last_staleness_per_worker"]]
+            extra.update({"async_updates": st["async_updates"], "rejected_updates": st["rejected_updates"],
+                          "average_gradient_staleness": round(sum(last) / max(1, len(last)), 2),
+                          "max_staleness_observed": max(last) if last else 0,
+                          "running_mean_staleness": round(st["running_mean_staleness"], 4),
+                          "running_max_staleness": st["running_max_staleness"],
+                          "staleness_histogram": st["staleness_histogram"], "torn_pulls": st["torn_pulls"]})
+        return M.server_final_metrics(mode=self.cfg.mode, total_workers=self.job.world, total_time=total,
+                                      global_step=steps, total_updates=steps,
+                                      gradients_processed=steps * (self.job.world if self.cfg.mode == "sync" else 1),
+                                      avg_update_time=0.0, learning_rate=self.cfg.lr, extra=extra)
+
+    def finish(self) -> dict:
+        """Emit SERVER_FINAL_METRICS exactly once."""
+        if self._final is None:
+            self._final = self.metrics()
+            M.emit(self._final, self.cfg.metrics_dir, f"server_shard{self.job.rank}")
+        return self._final
+
+
+class LossHandle:
+    """Result of a step: the loss lands in pinned host memory; ``item()`` waits for that copy only."""
+
+    def __init__(self, host: torch.Tensor, event: torch.cuda.Event):
+        self.host, self.event = host, event
+
+    def item(self) -> float:
+        self.event.synchronize()
+        return float(self.host[0])
+
+    def correct(self) -> int:
+        self.event.synchronize()
+        return int(self.host[1])
+
+
+class Worker:
+    """This rank's worker: forward/backward on the local replica + push/pull against all shards."""
+
+    def __init__(self, job: Job):
+        self.job, self.ps, self.cfg = job, job.ps, job.cfg
+        self.rank, self.world = job.rank, job.world
+        self.worker_id, self.total_workers = job.rank, job.world      # rank == id: never out of range (Q10)
+        self.local_step_counter = 0
+        self.images_seen = 0
+        self.epoch_times: List[float] = []
+        self.accuracies: List[float] = []
+        self.training_start_time: Optional[float] = None
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self._ring = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(4)]
+        self._events = [torch.cuda.Event() for _ in range(4)]
+        self.engine_kind = self.cfg.engine
+        if self.engine_kind == "native":
+            from .models.engine import ResNetEngine
+            self.engine = ResNetEngine(job.layout, self.ps.wbf16[self.rank], self.ps.small[self.rank],
+                                       self.ps.grad[self.rank], batch=self.cfg.batch_size,
+                                       image_size=self.cfg.image_size, num_classes=self.cfg.num_classes,
+                                       device=job.device)
+            self.engine.load_bn_buffers(job.model_cpu.state_dict())
+        else:
+            from .models.torch_engine import TorchEngine
+            self.engine = TorchEngine(job.layout, self.ps.wbf16[self.rank], self.ps.small[self.rank],
+                                      self.ps.grad[self.rank], job.model_cpu, batch=self.cfg.batch_size,
+                                      image_size=self.cfg.image_size, device=job.device)
+        self._accum = 0
+
+    # ------------------------------------------------------------------ the step
+    def _exchange(self) -> None:
+        """Everything after backward: push -> (barrier, reduce, SGD | ring, staleness apply) -> pull."""
+        if self.cfg.mode == "sync":
+            self.ps.push_sync()
+            self.ps.pull()
+        else:
+            self.ps.push_async()
+            self.ps.serve_async()
+            self.ps.pull_async()
+
+    def _build_graph(self) -> None:
+        self.ps.use_device_counters(True)
+        saved = {k: v.clone() for k, v in self.engine.bn_buffers().items()}   # warm-up must not count as a step
+        self.engine.capture(extra=self._exchange if self.cfg.sync_steps == 1 else None)
+        for k, v in self.engine.bn_buffers().items():
+            v.copy_(saved[k])
+        # capture ran one eager warm-up step on the engine only: clear what it accumulated
+        self.ps.grad[self.rank].zero_()
+        self.graph = self.engine.graph
+        torch.cuda.synchronize(self.job.device)
+
+    def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> LossHandle:
+        """One local batch.  `images` fp32 [B,3,S,S] and `labels` int64 [B] (host, ideally pinned)."""
+        use_graph = self.cfg.use_cuda_graph and self.engine_kind == "native"
+        if use_graph and self.graph is None:
+            self._build_graph()
+        self.engine.load_batch(images, labels)
+        fused_exchange = use_graph and self.cfg.sync_steps == 1
+        if use_graph:
+            self.graph.replay()
+        else:
+            self.engine.forward_backward()
+        self._accum += 1
+        if self._accum >= self.cfg.sync_steps:
+            if not fused_exchange:
+                if self._accum > 1:
+                    self.ps.grad[self.rank].div_(self._accum)       # Q12: accumulate, not discard
+                self._exchange()
+            if self.cfg.mode == "sync":
+                self.ps.step += 1
+            self._accum = 0
+        slot = self.local_step_counter % len(self._ring)
+        self._ring[slot].copy_(self.engine.out, non_blocking=True)
+        self._events[slot].record()
+        self.local_step_counter += 1
+        self.images_seen += int(labels.numel())
+        return LossHandle(self._ring[slot], self._events[slot])
+
+    # ------------------------------------------------------------------ evaluation
+    @torch.no_grad()
+    def evaluate(self, loader: Iterable[Tuple[torch.Tensor, torch.Tensor]], max_batches: Optional[int] = None,
+                 shard: bool = False) -> float:
+        """Top-1 accuracy in percent with running BN statistics (reference: worker.py:313-331).
+        shard=True evaluates batches rank::world and all-reduces the counts."""
+        correct = total = 0
+        B = self.cfg.batch_size
+        for i, (x, y) in enumerate(loader):
+            if max_batches is not None and i >= max_batches:
+                break
+            if shard and i % self.world != self.rank:
+                continue
+            n = int(y.numel())
+            if n != B:                                   # static shapes: pad the tail batch
+                xp = torch.zeros(B, *x.shape[1:], dtype=x.dtype)
+                yp = torch.full((B,), -1, dtype=y.dtype)
+                xp[:n], yp[:n] = x, y
+                x, y = xp, yp
+            correct += self.engine.eval_batch(x, y)
+            total += n
+        if shard and self.world > 1:
+            import torch.distributed as dist
+            t = torch.tensor([correct, total], device=self.job.device, dtype=torch.int64)
+            dist.all_reduce(t)
+            correct, total = int(t[0]), int(t[1])
+        acc = 100.0 * correct / max(1, total)
+        self.accuracies.append(acc)
+        return acc
+
+    # ------------------------------------------------------------------ loop (reference: worker.py:350-403)
+    def run_training(self, train_loader, test_loader=None, epochs: Optional[int] = None,
+                     max_steps: Optional[int] = None, eval_batches: Optional[int] = None) -> dict:
+        self.training_start_time = time.time()
+        epochs = self.cfg.epochs if epochs is None else epochs
+        done = False
+        last = None
+        for _ in range(epochs):
+            t0 = time.time()
+            for x, y in train_loader:
+                if int(y.numel()) != self.cfg.batch_size:
+                    continue                                # static shapes: drop the ragged tail batch
+                last = self.train_step(x, y)
+                if max_steps is not None and self.local_step_counter >= max_steps:
+                    done = True
+                    break
+            if last is not None:
+                last.item()
+            torch.cuda.synchronize(self.job.device)
+            self.epoch_times.append(time.time() - t0)       # excludes evaluation (Q17)
+            if test_loader is not None:
+                self.evaluate(test_loader, eval_batches)
+            if done:
+                break
+        return self.finish()
+
+    def drain(self, rounds: int = 2) -> None:
+        """Async mode: apply arrivals that landed after this rank's last step (end of job)."""
+        if self.cfg.mode != "async":
+            return
+        for _ in range(rounds):
+            self.job.barrier()
+            self.ps.serve_async()
+        self.job.barrier()
+
+    def finish(self) -> dict:
+        self.drain()
+        total = time.time() - (self.training_start_time or time.time())
+        train_time = sum(self.epoch_times)
+        rec = M.worker_final_metrics(
+            worker_id=self.worker_id, total_workers=self.total_workers, total_time=total,
+            epoch_times=self.epoch_times, accuracies=self.accuracies, local_steps=self.local_step_counter,
+            batch_size=self.cfg.batch_size, learning_rate=self.cfg.lr, num_epochs=self.cfg.epochs,
+            extra={"images_per_second": round(self.images_seen / train_time, 2) if train_time > 0 else 0.0,
+                   "transport": "nvlink-p2p", "engine": self.engine_kind, "mode": self.cfg.mode,
+                   "push_bytes_per_step": self.ps.bytes_per_push(), "pull_bytes_per_step": self.ps.bytes_per_pull()})
+        M.emit(rec, self.cfg.metrics_dir, "worker")
+        return rec
+
+    # ------------------------------------------------------------------ BN buffers (Q5)
+    def bn_buffers_for_checkpoint(self) -> Dict[str, torch.Tensor]:
+        bufs = {k: v.detach().clone() for k, v in self.engine.bn_buffers().items()}
+        policy = self.cfg.bn_buffer_policy
+        if policy == "reference":                      # never updated on the server: initial values
+            init = self.job.model_cpu.state_dict()
+            return {k: init[k].clone() for k in bufs}
+        if policy == "mean" and self.world > 1:
+            import torch.distributed as dist
+            for k, v in bufs.items():
+                if v.dtype.is_floating_point:
+                    dist.all_reduce(v)
+                    v /= self.world
+                else:
+                    dist.all_reduce(v, op=dist.ReduceOp.MAX)
+        return {k: v.cpu() for k, v in bufs.items()}

@@ -1,0 +1,339 @@
+"""ResNet-18 training engine built from the hand-written sm_100a kernels.
+
+This is the hot path on B200: a *static* schedule of kernel launches over pre-allocated NHWC bf16
+buffers -- implicit-GEMM convs on tcgen05/TMEM fed by TMA (ops/conv.py, csrc/conv_tc.cu), fused
+BatchNorm(+residual)+ReLU (csrc/bn.cu), fused avg-pool + FC + cross-entropy head (csrc/head.cu) --
+captured once into a CUDA graph and replayed every step.  No autograd, no cuDNN/cuBLAS, no tracing
+compiler.  Same network as ``models/resnet.py`` (reference: src/parameter_server/server.py:21-76);
+weights are read from the worker's bf16 arena and gradients are accumulated into the flat fp32
+gradient arena, both laid out by ``store/shardmap.py`` -- exactly what the Push/Pull kernels move.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from dataclasses import dataclass, field
+from typing import Callable, Dict, List, Optional, Tuple
+
+import torch
+
+from ..ops import _lib as L
+from ..ops.conv import ConvPlan
+from ..store.shardmap import STEM_PITCH, Layout
+from .resnet import BLOCKS_PER_STAGE, STAGE_STRIDES, STAGE_WIDTHS
+
+_declared = False
+
+
+def _decl() -> None:
+    global _declared
+    if _declared:
+        return
+    P, i32, i64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_float
+    L.declare("dps_bn_forward", i32, [P, P, P, P, P, P, P, P, P, P, P, i64, i32, i32, i32, f32, f32, P])
+    L.declare("dps_bn_backward", i32, [P, P, P, P, P, P, P, P, P, P, P, i64, i32, i32, P])
+    L.declare("dps_head_forward_backward", i32, [P] * 12 + [i32, i32, i32, i32, i32, P])
+    L.declare("dps_stem_im2col", i32, [P, P, i32, i32, i32, P])
+    _declared = True
+
+
+def _p(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+@dataclass
+class _BN:
+    name: str                 # state_dict prefix, e.g. 'layer1.0.bn1'
+    C: int
+    P: int
+    gamma: torch.Tensor
+    beta: torch.Tensor
+    dgamma: torch.Tensor
+    dbeta: torch.Tensor
+    stats: torch.Tensor       # [2C] fwd sums (zeroed per step)
+    bsums: torch.Tensor       # [2C] bwd sums (zeroed per step)
+    mean: torch.Tensor
+    rstd: torch.Tensor
+    running_mean: torch.Tensor
+    running_var: torch.Tensor
+    num_batches: torch.Tensor
+
+
+class ResNetEngine:
+    BN_EPS = 1e-5
+    BN_MOMENTUM = 0.1
+
+    def __init__(self, layout: Layout, wbf16: torch.Tensor, small: torch.Tensor, grad: torch.Tensor,
+                 batch: int, image_size: int = 32, num_classes: int = 100, device: Optional[torch.device] = None):
+        _decl()
+        self.lib = L.lib()
+        self.layout, self.wbf16, self.small, self.grad = layout, wbf16, small, grad
+        self.N, self.S, self.K = batch, image_size, num_classes
+        self.dev = device or wbf16.device
+        self.bns: List[_BN] = []
+        self.fwd: List[Callable[[], None]] = []
+        self.bwd: List[Callable[[], None]] = []
+        self.evalf: List[Callable[[], None]] = []
+        self.n_launch_fwd = self.n_launch_bwd = 0
+        self._keep: List[object] = []
+        self._scratch_need = 0
+        self._scratch_slices: List[Tuple[int, int]] = []
+        self._build()
+        self.graph: Optional[torch.cuda.CUDAGraph] = None
+
+    # ------------------------------------------------------------------ helpers
+    def _bf(self, *shape) -> torch.Tensor:
+        return torch.zeros(*shape, dtype=torch.bfloat16, device=self.dev)
+
+    def _w(self, name: str) -> torch.Tensor:
+        e = self.layout.entries[name]
+        return self.wbf16[e.offset: e.offset + e.span]
+
+    def _g(self, name: str) -> torch.Tensor:
+        e = self.layout.entries[name]
+        return self.grad[e.offset: e.offset + e.span]
+
+    def _sm(self, name: str) -> torch.Tensor:
+        e = self.layout.entries[name]
+        return self.small[e.offset: e.offset + e.span]
+
+    def _stream(self) -> C.c_void_p:
+        return C.c_void_p(L.stream_ptr())
+
+    def _make_bn(self, name: str, Cc: int, P: int) -> _BN:
+        f = lambda n: torch.zeros(n, dtype=torch.float32, device=self.dev)
+        off = self._scratch_need
+        self._scratch_need += 4 * Cc
+        bn = _BN(name, Cc, P, self._sm(name + ".weight"), self._sm(name + ".bias"), self._g(name + ".weight"),
+                 self._g(name + ".bias"), None, None, f(Cc), f(Cc), f(Cc), torch.ones(Cc, device=self.dev),
+                 torch.zeros((), dtype=torch.int64, device=self.dev))
+        self._scratch_slices.append((off, Cc))
+        self.bns.append(bn)
+        return bn
+
+    # ------------------------------------------------------------------ op emitters
+    def _bn_fwd(self, bn: _BN, x, y, residual, relu, training):
+        L.check(self.lib.dps_bn_forward(_p(x), _p(bn.stats), _p(bn.gamma), _p(bn.beta), _p(residual), _p(y),
+                                        _p(bn.mean), _p(bn.rstd), _p(bn.running_mean), _p(bn.running_var),
+                                        _p(bn.num_batches), bn.P, bn.C, int(relu), int(training), self.BN_EPS,
+                                        self.BN_MOMENTUM, self._stream()), "bn_forward")
+
+    def _bn_bwd(self, bn: _BN, dy, y, x, dz, dx, relu):
+        L.check(self.lib.dps_bn_backward(_p(dy), _p(y), _p(x), _p(bn.mean), _p(bn.rstd), _p(bn.gamma), _p(dz),
+                                         _p(bn.bsums), _p(dx), _p(bn.dgamma), _p(bn.dbeta), bn.P, bn.C, int(relu),
+                                         self._stream()), "bn_backward")
+
+    # ------------------------------------------------------------------ graph construction
+    def _conv_bn_unit(self, x, prefix_conv, prefix_bn, *, H, Cin, Cout, R, stride, relu, residual=None, stem=False):
+        """conv -> BN(+residual)(+ReLU).  Returns dict with buffers and registers fwd/eval launches."""
+        Ho = H // stride
+        P = self.N * Ho * Ho
+        c = self._bf(self.N, Ho, Ho, Cout)
+        a = self._bf(self.N, Ho, Ho, Cout)
+        bn = self._make_bn(prefix_bn, Cout, P)
+        unit = dict(x=x, c=c, a=a, bn=bn, H=H, Cin=Cin, Cout=Cout, R=R, stride=stride, relu=relu, stem=stem,
+                    wname=prefix_conv + ".weight", residual=residual)
+        return unit
+
+    def _finalize_unit_fwd(self, u):
+        """Create plans (needs bn.stats allocated) and append forward / eval launches."""
+        bn = u["bn"]
+        kw = dict(N=self.N, H=u["H"], W=u["H"], Cin=u["Cin"], Cout=u["Cout"], R=u["R"], stride=u["stride"])
+        if u["stem"]:
+            kw.update(w_cols=STEM_PITCH, w_pitch=STEM_PITCH)
+        w = self._w(u["wname"])
+        plan = ConvPlan.fprop(u["x"], w, u["c"], stats=bn.stats, **kw)
+        plan_eval = ConvPlan.fprop(u["x"], w, u["c"], stats=None, **kw)
+        self._keep += [plan, plan_eval]
+        u["fprop"] = plan
+        res = u["residual"]
+        self.fwd.append(plan.run)
+        self.fwd.append(lambda bn=bn, u=u, res=res: self._bn_fwd(bn, u["c"], u["a"], res, u["relu"], True))
+        self.evalf.append(plan_eval.run)
+        self.evalf.append(lambda bn=bn, u=u, res=res: self._bn_fwd(bn, u["c"], u["a"], res, u["relu"], False))
+
+    def _build(self) -> None:
+        N, S = self.N, self.S
+        dev = self.dev
+        self.images = torch.zeros(N, 3, S, S, dtype=torch.float32, device=dev)
+        self.labels = torch.zeros(N, dtype=torch.int64, device=dev)
+        self.col = self._bf(N * S * S, 64)
+        units: List[dict] = []
+        # stem as a K=64 GEMM over im2col rows
+        stem = self._conv_bn_unit(self.col.view(N, S, S, 64), "conv1", "bn1", H=S, Cin=64, Cout=STAGE_WIDTHS[0], R=1,
+                                  stride=1, relu=True, stem=True)
+        units.append(stem)
+        x, H, Cin = stem["a"], S, STAGE_WIDTHS[0]
+        blocks = []
+        for li, (Cout, s0) in enumerate(zip(STAGE_WIDTHS, STAGE_STRIDES), start=1):
+            for b in range(BLOCKS_PER_STAGE):
+                stride = s0 if b == 0 else 1
+                pre = f"layer{li}.{b}"
+                u1 = self._conv_bn_unit(x, pre + ".conv1", pre + ".bn1", H=H, Cin=Cin, Cout=Cout, R=3, stride=stride,
+                                        relu=True)
+                Ho = H // stride
+                us = None
+                if stride != 1 or Cin != Cout:
+                    us = self._conv_bn_unit(x, pre + ".shortcut.0", pre + ".shortcut.1", H=H, Cin=Cin, Cout=Cout, R=1,
+                                            stride=stride, relu=False)
+                res = us["a"] if us is not None else x
+                u2 = self._conv_bn_unit(u1["a"], pre + ".conv2", pre + ".bn2", H=Ho, Cin=Cout, Cout=Cout, R=3, stride=1,
+                                        relu=True, residual=res)
+                # forward order: conv1/bn1, shortcut (so its output exists before bn2), conv2/bn2
+                units += [u1] + ([us] if us is not None else []) + [u2]
+                blocks.append(dict(x=x, u1=u1, u2=u2, us=us, H=H, Ho=Ho, Cin=Cin, Cout=Cout, stride=stride))
+                x, H, Cin = u2["a"], Ho, Cout
+        self.units, self.blocks = units, blocks
+        self.feat, self.featH, self.F = x, H, Cin
+
+        # per-step zeroed scratch: [fwd stats | bwd sums] for every BN
+        self.scratch = torch.zeros(self._scratch_need, dtype=torch.float32, device=dev)
+        for bn, (off, Cc) in zip(self.bns, self._scratch_slices):
+            bn.stats = self.scratch[off: off + 2 * Cc]
+            bn.bsums = self.scratch[off + 2 * Cc: off + 4 * Cc]
+
+        # ---------------- forward schedule ----------------
+        self.fwd.append(lambda: self.scratch.zero_())
+        im2col = lambda: L.check(self.lib.dps_stem_im2col(_p(self.images), _p(self.col), N, S, S, self._stream()),
+                                 "stem_im2col")
+        self.fwd.append(im2col)
+        self.evalf.append(im2col)
+        for u in units:
+            self._finalize_unit_fwd(u)
+
+        # head
+        HW = self.featH * self.featH
+        self.pooled = torch.zeros(N, self.F, device=dev)
+        self.dlogits = torch.zeros(N, 128, device=dev)
+        self.loss_n = torch.zeros(N, device=dev)
+        self.correct_n = torch.zeros(N, dtype=torch.int32, device=dev)
+        self.out = torch.zeros(2, device=dev)             # [mean loss, #correct]
+        self.d_feat = self._bf(N, self.featH, self.featH, self.F)
+        fcw, fcb = self._w("fc.weight"), self._sm("fc.bias")
+        gw, gb = self._g("fc.weight"), self._g("fc.bias")
+
+        def head(training: bool):
+            L.check(self.lib.dps_head_forward_backward(
+                _p(self.feat), _p(fcw), _p(fcb), _p(self.labels), _p(self.pooled), _p(self.dlogits), _p(self.loss_n),
+                _p(self.correct_n), _p(self.d_feat), _p(gw), _p(gb), _p(self.out), N, HW, self.F, self.K,
+                int(training), self._stream()), "head")
+        self.fwd.append(lambda: head(True))
+        self.evalf.append(lambda: head(False))
+
+        # ---------------- backward schedule ----------------
+        g_out = self.d_feat
+        for blk in reversed(blocks):
+            u1, u2, us = blk["u1"], blk["u2"], blk["us"]
+            Cin, Cout, H, Ho, stride = blk["Cin"], blk["Cout"], blk["H"], blk["Ho"], blk["stride"]
+            g_c2 = self._bf(N, Ho, Ho, Cout)
+            g_a1 = self._bf(N, Ho, Ho, Cout)
+            g_c1 = self._bf(N, Ho, Ho, Cout)
+            g_x = self._bf(N, H, H, Cin)
+            dz2 = g_out                                        # masked gradient written in place
+            self.bwd.append(lambda u2=u2, g_out=g_out, g_c2=g_c2:
+                            self._bn_bwd(u2["bn"], g_out, u2["a"], u2["c"], g_out, g_c2, True))
+            kw2 = dict(N=N, H=Ho, W=Ho, Cin=Cout, Cout=Cout, R=3, stride=1)
+            p_w2 = ConvPlan.wgrad(u1["a"], g_c2, self._g(u2["wname"]), **kw2)
+            p_d2 = ConvPlan.dgrad(g_c2, self._w(u2["wname"]), g_a1, **kw2)
+            self.bwd += [p_w2.run, p_d2.run]
+            self.bwd.append(lambda u1=u1, g_a1=g_a1, g_c1=g_c1:
+                            self._bn_bwd(u1["bn"], g_a1, u1["a"], u1["c"], g_a1, g_c1, True))
+            kw1 = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=3, stride=stride)
+            p_w1 = ConvPlan.wgrad(blk["x"], g_c1, self._g(u1["wname"]), **kw1)
+            self.bwd.append(p_w1.run)
+            self._keep += [p_w2, p_d2, p_w1]
+            if us is None:
+                p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=dz2, **kw1)
+                self.bwd.append(p_d1.run)
+                self._keep.append(p_d1)
+            else:
+                p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, **kw1)
+                g_cs = self._bf(N, Ho, Ho, Cout)
+                kws = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=1, stride=stride)
+                p_ws = ConvPlan.wgrad(blk["x"], g_cs, self._g(us["wname"]), **kws)
+                p_ds = ConvPlan.dgrad(g_cs, self._w(us["wname"]), g_x, addend=g_x, **kws)
+                self.bwd.append(p_d1.run)
+                self.bwd.append(lambda us=us, dz2=dz2, g_cs=g_cs:
+                                self._bn_bwd(us["bn"], dz2, None, us["c"], None, g_cs, False))
+                self.bwd += [p_ws.run, p_ds.run]
+                self._keep += [p_d1, p_ws, p_ds]
+            g_out = g_x
+        # stem
+        g_c0 = self._bf(N, S, S, STAGE_WIDTHS[0])
+        self.bwd.append(lambda stem=stem, g_out=g_out, g_c0=g_c0:
+                        self._bn_bwd(stem["bn"], g_out, stem["a"], stem["c"], g_out, g_c0, True))
+        p_w0 = ConvPlan.wgrad(self.col.view(N, S, S, 64), g_c0, self._g("conv1.weight"), N=N, H=S, W=S, Cin=64,
+                              Cout=STAGE_WIDTHS[0], R=1, stride=1, valid_cols=STEM_PITCH, dw_pitch=STEM_PITCH)
+        self.bwd.append(p_w0.run)
+        self._keep.append(p_w0)
+        # launches per step (bn_backward and head are two kernels each)
+        self.kernels_per_step = self._count_kernels()
+
+    def _count_kernels(self) -> int:
+        n_bn = len(self.bns)
+        n_conv = len(self.units)
+        fwd = 1 + 1 + n_conv + n_bn + 2                      # memset, im2col, convs, bn, head(2)
+        n_dgrad = n_conv - 1
+        bwd = 2 * n_bn + n_conv + n_dgrad
+        return fwd + bwd
+
+    # ------------------------------------------------------------------ execution
+    def load_batch(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        self.images.copy_(images, non_blocking=True)
+        self.labels.copy_(labels, non_blocking=True)
+
+    def forward_backward(self) -> None:
+        for f in self.fwd:
+            f()
+        for f in self.bwd:
+            f()
+
+    def forward_eval(self) -> None:
+        for f in self.evalf:
+            f()
+
+    def capture(self, extra: Optional[Callable[[], None]] = None, warmup: int = 1) -> None:
+        """Capture forward+backward (+ `extra`, e.g. push/pull) into one CUDA graph."""
+        s = torch.cuda.Stream(device=self.dev)
+        s.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(s):
+            for _ in range(warmup):
+                self.forward_backward()
+        torch.cuda.current_stream().wait_stream(s)
+        torch.cuda.synchronize(self.dev)
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            self.forward_backward()
+            if extra is not None:
+                extra()
+        self.graph = g
+
+    @torch.no_grad()
+    def eval_batch(self, images: torch.Tensor, labels: torch.Tensor) -> int:
+        """Forward in eval mode (running BN statistics); returns the number of correct top-1 predictions.
+        Labels < 0 mark padding rows and never count as correct."""
+        self.load_batch(images, labels)
+        self.forward_eval()
+        return int(self.out[1].item())
+
+    def step(self) -> None:
+        if self.graph is not None:
+            self.graph.replay()
+        else:
+            self.forward_backward()
+
+    # ------------------------------------------------------------------ state
+    def bn_buffers(self) -> Dict[str, torch.Tensor]:
+        out = {}
+        for bn in self.bns:
+            out[bn.name + ".running_mean"] = bn.running_mean
+            out[bn.name + ".running_var"] = bn.running_var
+            out[bn.name + ".num_batches_tracked"] = bn.num_batches
+        return out
+
+    def load_bn_buffers(self, sd) -> None:
+        for k, v in self.bn_buffers().items():
+            if k in sd:
+                v.copy_(torch.as_tensor(sd[k]).to(v.device, v.dtype))
+
+    def activation_bytes(self) -> int:
+        return sum(u["c"].numel() * 2 + u["a"].numel() * 2 for u in self.units)

@@ -40,6 +40,7 @@ class DpsTables(C.Structure):
         ("grad", _PtrArray), ("master", _PtrArray), ("mom", _PtrArray), ("stage", _PtrArray),
         ("ring", _PtrArray), ("wbf16", _PtrArray), ("small", _PtrArray), ("pub", _PtrArray),
         ("pubsmall", _PtrArray), ("flags", _PtrArray),
+        ("step_ctr", _P), ("lr_ptr", _P),
     ]
 
 
@@ -65,7 +66,7 @@ def _declare(lib: C.CDLL) -> None:
         "dps_enable_peer": (i32, [i32, i32]),
         "dps_push_sync": (i32, [TP, u32, f32, f32, f32, i32, i32, u64, _P]),
         "dps_pull_bcast": (i32, [TP, u32, i32, _P]),
-        "dps_wait_pull": (i32, [TP, i32, u32, i32, u64, _P]),
+        "dps_wait_pull": (i32, [TP, i32, u32, i32, u64, i32, _P]),
         "dps_push_async": (i32, [TP, i32, u32, i32, u64, _P]),
         "dps_async_apply": (i32, [TP, i32, i32, i32, f32, f32, i32, f32, f32, f32, i32, _P]),
         "dps_pull_async": (i32, [TP, i32, i32, _P]),

@@ -88,11 +88,28 @@ class DevicePS:
             t.grad[r] = self.grad[r].data_ptr()
             t.master[r] = self.master[r].data_ptr()
             t.mom[r] = self.mom[r].data_ptr()
+        # device-resident round counters + learning rate (graph replay needs no baked-in step / lr)
+        self.step_ctr = torch.zeros(4, dtype=torch.int32, device=dev)
+        self.lr_dev = torch.full((1,), float(cfg.lr), dtype=torch.float32, device=dev)
+        self.device_counters = False
         self.tables = t
         self._tp = C.byref(self.tables)
         self.step = 0                       # sync round / pull sequence number
         self.async_steps = {r: 0 for r in self.local}
         self.launches = 0
+
+    def use_device_counters(self, on: bool = True) -> None:
+        """Read round number and lr from device memory (required before CUDA-graph capture)."""
+        assert not self.emulate or not on, "device counters are per-process; not used in emulation"
+        self.step_ctr[0] = self.step
+        self.step_ctr[1] = self.async_steps.get(self.rank, 0)
+        self.tables.step_ctr = self.step_ctr.data_ptr() if on else None
+        self.tables.lr_ptr = self.lr_dev.data_ptr() if on else None
+        self.device_counters = on
+
+    def set_lr(self, lr: float) -> None:
+        self.cfg = self.cfg.replace(lr=lr)
+        self.lr_dev.fill_(lr)
 
     # ------------------------------------------------------------------ state
     def load_master(self, flat_global: torch.Tensor) -> None:
@@ -145,7 +162,7 @@ class DevicePS:
         if wait:
             for r in self.local:
                 L.check(self.lib.dps_wait_pull(self._tp, r, self.step, self.ctas, self.timeout_ns,
-                                               L.stream_ptr(stream)), "wait_pull")
+                                               int(self.device_counters), L.stream_ptr(stream)), "wait_pull")
                 self.launches += 1
 
     def sync_round(self, lr: Optional[float] = None, stream=None) -> None:

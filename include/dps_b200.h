@@ -72,6 +72,11 @@ typedef struct DpsTables {
   uint16_t* pub[DPS_MAX_RANKS];              /* owner: published bf16 shard [E] (async pulls)        */
   float* pubsmall[DPS_MAX_RANKS];        /* owner: published fp32 small prefix [n_small]         */
   uint32_t* flags[DPS_MAX_RANKS];        /* flag block [DPS_FLAG_WORDS]                          */
+  /* Optional device-resident step counters and learning rate, so a captured CUDA graph can be replayed:
+   * when non-NULL they override the `step` / `lr` arguments.  step_ctr[0] = sync round (bumped by
+   * dps_wait_pull with bump=1), step_ctr[1] = this rank's async push count (bumped by dps_async_apply). */
+  uint32_t* step_ctr;
+  const float* lr_ptr;
 } DpsTables;
 
 const char* dps_last_error(void);
@@ -92,7 +97,7 @@ int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, f
 /* reference: server.py:213-230 + worker.py:233-262 (FetchParameters + load_state_dict) */
 int dps_pull_bcast(const DpsTables* T, unsigned step, int ctas, void* stream);
 int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_per_owner, unsigned long long timeout_ns,
-                  void* stream);
+                  int bump, void* stream);
 /* reference: server.py:290-304,171-186 (async apply-on-arrival with staleness weighting) */
 int dps_push_async(const DpsTables* T, int rank, unsigned step, int ctas, unsigned long long timeout_ns,
                    void* stream);

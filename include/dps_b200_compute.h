@@ -28,6 +28,28 @@ int dps_conv_plan_run(void* plan, void* stream);
 int dps_conv_plan_destroy(void* plan);
 int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* smem_bytes);
 
+/* ---- fused BatchNorm(+residual)+ReLU (reference: nn.BatchNorm2d + torch.relu + `out += shortcut(x)`,
+ *      server.py:25-40,49,67-68).  x, residual, y: [P][C] bf16 (NHWC flattened); stats = [2C] sum / sumsq
+ *      produced by the conv epilogue.  training == 0 normalises with the running statistics. ---- */
+int dps_bn_forward(const void* x, const float* stats, const float* gamma, const float* beta, const void* residual,
+                   void* y, float* save_mean, float* save_rstd, float* running_mean, float* running_var,
+                   long long* num_batches, long long P, int C, int relu, int training, float eps, float momentum,
+                   void* stream);
+/* sums: [2C] fp32 scratch, zero on entry.  dz (masked gradient) may alias dy.  dgamma/dbeta are accumulated. */
+int dps_bn_backward(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
+                    const float* gamma, void* dz, float* sums, void* dx, float* dgamma, float* dbeta, long long P,
+                    int C, int relu, void* stream);
+
+/* ---- fused head: avg-pool + Linear + softmax cross-entropy, forward and backward (reference:
+ *      server.py:56-57,73-75; worker.py:133,341-345).  act: [N][HW][F] bf16; w: [K][F] bf16; out[0] = mean loss,
+ *      out[1] = number of correct top-1 predictions.  dlogits scratch is [N][128]; dw/db are accumulated. ---- */
+int dps_head_forward_backward(const void* act, const void* w, const float* bias, const long long* labels,
+                              float* pooled, float* dlogits, float* loss_n, int* correct_n, void* d_act, float* dw,
+                              float* db, float* out, int N, int HW, int F, int K, int training, void* stream);
+
+/* ---- stem input staging: fp32 NCHW images -> bf16 im2col rows [N*H*W][64] (27 valid columns) ---- */
+int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
