@@ -86,11 +86,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
     const float* __restrict__ mean, const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
     double* __restrict__ sums, long long P, int C, int relu) {
-  // fp64 accumulation across threads/CTAs: the result is independent of atomic ordering to ~1e-16, so the
-  // activation gradients of a step are reproducible run to run (bf16 re-rounding would amplify fp32 jitter)
-  __shared__ double s_sum[2 * kMaxC];
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) s_sum[c] = 0.0;
-  __syncthreads();
+  // Cross-thread reduction in a fixed order (no shared-memory atomics), then ONE fp64 global atomic per channel
+  // per CTA: the result is independent of atomic ordering to ~1e-16, so the activation gradients of a step are
+  // reproducible run to run (bf16 re-rounding would otherwise amplify fp32 summation jitter).
+  __shared__ float s_part[kBnThreads * 16];            // [row slot][2C] partials
   const int cg = C / 8;                               // channel groups; 256 % cg == 0
   const int my_cg = threadIdx.x % cg;
   const int rows_per_pass = blockDim.x / cg;
@@ -115,13 +114,18 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
       a_dzx[i] += g.v[i] * (xv.v[i] - mu[i]) * rs[i];
     }
   }
+  const int slot = threadIdx.x / cg;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {
-    atomicAdd(&s_sum[c0 + i], (double)a_dz[i]);
-    atomicAdd(&s_sum[C + c0 + i], (double)a_dzx[i]);
+    s_part[slot * 2 * C + c0 + i] = a_dz[i];
+    s_part[slot * 2 * C + C + c0 + i] = a_dzx[i];
   }
   __syncthreads();
-  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) atomicAdd(sums + c, s_sum[c]);
+  for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
+    double acc = 0.0;
+    for (int k = 0; k < rows_per_pass; ++k) acc += (double)s_part[k * 2 * C + c];
+    atomicAdd(sums + c, acc);
+  }
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
