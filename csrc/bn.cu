@@ -201,3 +201,81 @@ DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const 
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------
+// BatchNorm backward for callers that must not allocate.
+//
+// dps_bn_backward() needs a [2*C] fp64 reduction scratch from its caller.  Some callers have nowhere to
+// get one: a serving or training process whose device memory was handed in full to a pool with a hard
+// budget at start-up (a later cudaMalloc fails or is forbidden by policy), a latency-critical loop where the
+// implicit device-wide synchronisation of cudaMalloc/cudaFree is not acceptable, or a hook / plug-in callback
+// that only receives its input and output buffers.  For them the scratch lives inside the library image:
+// one file-scope __device__ array of kNoAllocMaxC = 512 channels (2 * 512 doubles = 8 KiB), resident on every
+// GPU that loads the library until the process exits.
+//
+// Rules that follow from sharing one array:
+//   * the array keeps whatever the previous call left in it, so every call first clears the 2*C entries it
+//     is about to accumulate into (a memset on `stream`, ordered before the kernels);
+//   * two calls that can overlap on the GPU (different streams, or different host threads feeding different
+//     streams) race on the array -- serialise them on one stream or with events;
+//   * C above 512 is rejected with an error; nothing is truncated.
+//
+// Set-up: in host code `g_bn_noalloc_scratch` is only a stand-in for the symbol, not a device address, so
+// its address is resolved with cudaGetSymbolAddress the first time the entry point runs on a device (with
+// that device current), checked, cached per device and then passed to the kernels as an ordinary pointer.
+// Make that first call on each device before starting any stream capture.
+// ------------------------------------------------------------------------------------------
+namespace dps {
+constexpr int kNoAllocMaxC = 512;
+constexpr int kNoAllocMaxDevices = 64;
+static __device__ __align__(256) double g_bn_noalloc_scratch[2 * kNoAllocMaxC];
+}  // namespace dps
+
+#include <mutex>
+
+static int bn_noalloc_scratch_ptr(double** out) {
+  static std::mutex mu;
+  static double* resolved[kNoAllocMaxDevices] = {nullptr};
+  int dev = -1;
+  DPS_CHECK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= kNoAllocMaxDevices) DPS_FAIL(1, "bn_backward_noalloc: device index %d not supported", dev);
+  std::lock_guard<std::mutex> lock(mu);
+  if (resolved[dev] == nullptr) {
+    void* p = nullptr;
+    // once per device, with that device current: the symbol has a different address on every GPU
+    DPS_CHECK(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
+    if (p == nullptr) DPS_FAIL(1, "bn_backward_noalloc: cudaGetSymbolAddress returned a null address");
+    resolved[dev] = static_cast<double*>(p);
+  }
+  *out = resolved[dev];
+  return 0;
+}
+
+// Same contract and results as dps_bn_backward, minus the `sums` argument.  Calls no cudaMalloc / cudaFree and no
+// allocating library routine; the caller still passes every input and output buffer.
+DPS_API int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x, const float* mean,
+                                    const float* rstd, const float* gamma, void* dz, void* dx, float* dgamma,
+                                    float* dbeta, long long P, int C, int relu, void* stream) {
+  if (C > kNoAllocMaxC)
+    DPS_FAIL(1, "bn_backward_noalloc: C=%d exceeds the built-in scratch (max %d channels); use dps_bn_backward "
+                "with a caller-provided [2*C] fp64 buffer", C, kNoAllocMaxC);
+  if (C <= 0 || C % 8 || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
+  if (P <= 0) DPS_FAIL(1, "bn_backward_noalloc: P must be positive");
+  double* sums = nullptr;
+  if (int e = bn_noalloc_scratch_ptr(&sums)) return e;
+  cudaStream_t st = (cudaStream_t)stream;
+  // the shared array still holds the previous call's sums: clear exactly what this call accumulates into
+  DPS_CHECK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * (size_t)C, st));
+  const int rows_per_pass = kBnThreads / (C / 8);
+  long long want = (P + rows_per_pass - 1) / rows_per_pass;
+  const int g1 = (int)(want < 148 * 4 ? (want < 1 ? 1 : want) : 148 * 4);
+  bn_bwd_reduce_kernel<<<g1, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
+                                                  (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz, sums, P, C,
+                                                  relu);
+  DPS_CHECK(cudaGetLastError());
+  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, st>>>((const __nv_bfloat16*)(relu ? dz : dy),
+                                                                  (const __nv_bfloat16*)x, mean, rstd, gamma, sums,
+                                                                  (__nv_bfloat16*)dx, dgamma, dbeta, P, C);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}

@@ -40,6 +40,16 @@ int dps_bn_backward(const void* dy, const void* y, const void* x, const float* m
                     const float* gamma, void* dz, double* sums, void* dx, float* dgamma, float* dbeta, long long P,
                     int C, int relu, void* stream);
 
+/* No counterpart in the reference.  dps_bn_backward for callers that cannot allocate the [2*C] scratch
+ * (memory fully owned by a fixed-budget pool, loops that cannot take cudaMalloc's device-wide sync, hooks that
+ * only receive their inputs and outputs): the scratch is a built-in device array, max C = 512 channels
+ * (8 KiB per GPU, held until exit).  It is cleared on `stream` at the start of every call; calls that overlap
+ * on the GPU race on it.  The first call on a device resolves the array's address -- make it before any
+ * stream capture.  Larger C is rejected with an error.  Same outputs as dps_bn_backward. */
+int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
+                            const float* gamma, void* dz, void* dx, float* dgamma, float* dbeta, long long P, int C,
+                            int relu, void* stream);
+
 /* ---- fused head: avg-pool + Linear + softmax cross-entropy, forward and backward (reference:
  *      server.py:56-57,73-75; worker.py:133,341-345).  act: [N][HW][F] bf16; w: [K][F] bf16; out[0] = mean loss,
  *      out[1] = number of correct top-1 predictions.  dlogits scratch is [N][128]; dw/db are accumulated. ---- */
