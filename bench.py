@@ -182,7 +182,7 @@ def run_ours(args) -> dict:
     ps_launches = 3 if cfg.mode == "sync" else 4
     kernels = getattr(wk.engine, "kernels_per_step", 0)
     out = {
-        "metric": "ResNet-18 images/sec (%s mode, sharded PS)" % cfg.mode,
+        "metric": "ResNet-18 images/sec (%s mode, parameter server)" % cfg.mode,
         "value": round(value, 1), "unit": "images/sec", "n_gpus": world, "steps": K, "warmup": W,
         "ms_per_step": round(ms_dev / K, 4), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": round(value / PUBLISHED[cfg.mode], 1), "dtype": "bf16", "data": "synthetic",

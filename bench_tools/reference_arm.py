@@ -105,7 +105,7 @@ def run_reference(args) -> dict:
     timed = max(r["epoch_times_seconds"][-1] for r in recs)
     value = N * steps_per_epoch * B / timed
     return {
-        "metric": "ResNet-18 images/sec (%s mode, sharded PS)" % args.mode, "impl": "reference",
+        "metric": "ResNet-18 images/sec (%s mode, parameter server)" % args.mode, "impl": "reference",
         "value": round(value, 2), "unit": "images/sec", "n_gpus": N, "steps": steps_per_epoch, "warmup": W,
         "ms_per_step": round(timed / steps_per_epoch * 1e3, 2), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": round(value / PUBLISHED[args.mode], 3), "dtype": "fp32", "data": "synthetic",
