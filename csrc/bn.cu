@@ -66,19 +66,41 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
     }
   }
   __syncthreads();
+  // blockDim (256) is a multiple of C/8, so a thread always lands on the same 8 channels: keep their
+  // scale/shift in registers and issue kUnroll independent 16-byte loads per tensor before using any of them.
   const int cg = C / 8;
   const long long nvec = P * cg;
-  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(v % cg) * 8;
-    V8 a = unpack8(ld_nc_v4(x + v * 8));
-    V8 r = {};
-    if (residual != nullptr) r = unpack8(ld_nc_v4(residual + v * 8));
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = (int)(v0 % cg) * 8;
+  float sc[8], sh[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      float o = a.v[i] * s_scale[c0 + i] + s_shift[c0 + i] + r.v[i];
-      a.v[i] = relu ? fmaxf(o, 0.f) : o;
+  for (int i = 0; i < 8; ++i) { sc[i] = s_scale[c0 + i]; sh[i] = s_shift[c0 + i]; }
+  constexpr int kUnroll = 4;
+  for (long long v = v0; v < nvec; v += kUnroll * stride) {
+    uint4 xa[kUnroll], ra[kUnroll];
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long vv = v + j * stride;
+      if (vv < nvec) {
+        xa[j] = ld_nc_v4(x + vv * 8);
+        if (residual != nullptr) ra[j] = ld_nc_v4(residual + vv * 8);
+      }
     }
-    st_v4(y + v * 8, pack8(a));
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long vv = v + j * stride;
+      if (vv >= nvec) break;
+      V8 a = unpack8(xa[j]);
+      V8 r = {};
+      if (residual != nullptr) r = unpack8(ra[j]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        float o = a.v[i] * sc[i] + sh[i] + r.v[i];
+        a.v[i] = relu ? fmaxf(o, 0.f) : o;
+      }
+      st_v4(y + vv * 8, pack8(a));
+    }
   }
 }
 
@@ -97,21 +119,38 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
   float mu[8], rs[8], a_dz[8], a_dzx[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) { mu[i] = mean[c0 + i]; rs[i] = rstd[c0 + i]; a_dz[i] = 0.f; a_dzx[i] = 0.f; }
-  for (long long row = (long long)blockIdx.x * rows_per_pass + threadIdx.x / cg; row < P;
-       row += (long long)gridDim.x * rows_per_pass) {
-    const long long off = row * C + c0;
-    V8 g = unpack8(ld_nc_v4(dy + off));
-    V8 xv = unpack8(ld_nc_v4(x + off));
-    if (relu) {
-      V8 yv = unpack8(ld_nc_v4(y + off));
+  constexpr int kUnroll = 4;
+  const long long rstride = (long long)gridDim.x * rows_per_pass;
+  for (long long row = (long long)blockIdx.x * rows_per_pass + threadIdx.x / cg; row < P; row += kUnroll * rstride) {
+    uint4 ga[kUnroll], xa[kUnroll], ya[kUnroll];
 #pragma unroll
-      for (int i = 0; i < 8; ++i) g.v[i] = yv.v[i] > 0.f ? g.v[i] : 0.f;
-      st_v4(dz + off, pack8(g));
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long rr = row + j * rstride;
+      if (rr < P) {
+        const long long off = rr * C + c0;
+        ga[j] = ld_nc_v4(dy + off);
+        xa[j] = ld_nc_v4(x + off);
+        if (relu) ya[j] = ld_nc_v4(y + off);
+      }
     }
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      a_dz[i] += g.v[i];
-      a_dzx[i] += g.v[i] * (xv.v[i] - mu[i]) * rs[i];
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long rr = row + j * rstride;
+      if (rr >= P) break;
+      const long long off = rr * C + c0;
+      V8 g = unpack8(ga[j]);
+      V8 xv = unpack8(xa[j]);
+      if (relu) {
+        V8 yv = unpack8(ya[j]);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) g.v[i] = yv.v[i] > 0.f ? g.v[i] : 0.f;
+        st_v4(dz + off, pack8(g));
+      }
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        a_dz[i] += g.v[i];
+        a_dzx[i] += g.v[i] * (xv.v[i] - mu[i]) * rs[i];
+      }
     }
   }
   const int slot = threadIdx.x / cg;
@@ -150,13 +189,30 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
   __syncthreads();
   const int cg = C / 8;
   const long long nvec = P * cg;
-  for (long long v = (long long)blockIdx.x * blockDim.x + threadIdx.x; v < nvec; v += (long long)gridDim.x * blockDim.x) {
-    const int c0 = (int)(v % cg) * 8;
-    V8 g = unpack8(ld_nc_v4(dz + v * 8));
-    V8 xv = unpack8(ld_nc_v4(x + v * 8));
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  const int c0 = (int)(v0 % cg) * 8;
+  float ka[8], kb[8], kc[8];
 #pragma unroll
-    for (int i = 0; i < 8; ++i) g.v[i] = s_a[c0 + i] * g.v[i] + s_b[c0 + i] * xv.v[i] + s_c[c0 + i];
-    st_v4(dx + v * 8, pack8(g));
+  for (int i = 0; i < 8; ++i) { ka[i] = s_a[c0 + i]; kb[i] = s_b[c0 + i]; kc[i] = s_c[c0 + i]; }
+  constexpr int kUnroll = 4;
+  for (long long v = v0; v < nvec; v += kUnroll * stride) {
+    uint4 ga[kUnroll], xa[kUnroll];
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long vv = v + j * stride;
+      if (vv < nvec) { ga[j] = ld_nc_v4(dz + vv * 8); xa[j] = ld_nc_v4(x + vv * 8); }
+    }
+#pragma unroll
+    for (int j = 0; j < kUnroll; ++j) {
+      const long long vv = v + j * stride;
+      if (vv >= nvec) break;
+      V8 g = unpack8(ga[j]);
+      V8 xv = unpack8(xa[j]);
+#pragma unroll
+      for (int i = 0; i < 8; ++i) g.v[i] = ka[i] * g.v[i] + kb[i] * xv.v[i] + kc[i];
+      st_v4(dx + vv * 8, pack8(g));
+    }
   }
 }
 

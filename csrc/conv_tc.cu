@@ -34,7 +34,9 @@
 
 namespace dps {
 
-constexpr int kStages = 3;
+constexpr int kMinStages = 3;      // 2 CTAs / SM when the grid has several waves
+constexpr int kMaxStages = 6;      // 1 CTA / SM (grid <= one wave): deeper pipeline hides the L2->smem latency
+constexpr int kCtrlBytes = 1024;   // barriers + TMEM slot live in front of the stage buffers
 constexpr int kTileM = 128;         // pixels per CTA tile == UMMA M
 constexpr int kKBlock = 64;         // reduction elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kABytes = kTileM * kKBlock * 2;   // 16 KiB
@@ -53,6 +55,7 @@ struct ConvParams {
   int tiles_w, tiles_h;           // tiles along w and h (tiles along n = gridDim.x / (tiles_w*tiles_h))
   int red_blocks;                 // 64-wide reduction blocks per tap
   int ngroups;                    // parity groups (gridDim.z)
+  int nstages;                    // pipeline depth (kMinStages or kMaxStages)
   int ntaps[4];
   Tap taps[4][9];
   int oph[4], opw[4];             // output parity offsets per group
@@ -69,9 +72,8 @@ struct ConvSmem {
   static constexpr int kBBytes = BLOCK_N * kKBlock * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPitch = BLOCK_N * 2 + 16;                 // staging row pitch (bank-conflict free)
-  static constexpr int kBarOff = kStages * kStageBytes;
-  static constexpr int kTotal = kBarOff + 128 + 1024;             // + barriers + alignment slack
-  static_assert(kTileM * kPitch <= kStages * kStageBytes, "staging must fit in the pipeline buffers");
+  static constexpr int total(int nst) { return 1024 + kCtrlBytes + nst * kStageBytes; }   // 1024 = alignment slack
+  static_assert(kTileM * kPitch <= kMinStages * kStageBytes, "staging must fit in the pipeline buffers");
 };
 
 template <int BLOCK_N, bool B_MN>
@@ -81,10 +83,12 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   using S = ConvSmem<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
-  uint64_t* empty = full + kStages;
-  uint64_t* tmem_full = empty + kStages;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint8_t* stages = smem + kCtrlBytes;
+  const int nst = p.nstages;
 
   const int warp = threadIdx.x >> 5;
   const int grp = blockIdx.z;
@@ -104,7 +108,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   }
   if (warp == 1) {
     if (elect_one()) {
-      for (int s = 0; s < kStages; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      for (int s = 0; s < nst; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
       mbar_init(tmem_full, 1);
       fence_barrier_init();
     }
@@ -121,11 +125,11 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     // ===================== TMA producer =====================
     if (elect_one()) {
       for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % kStages, ph = (kb / kStages) & 1;
+        const int s = kb % nst, ph = (kb / nst) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         const Tap tp = p.taps[grp][kb / p.red_blocks];
         const int cb = kb % p.red_blocks;
-        uint8_t* a = smem + s * S::kStageBytes;
+        uint8_t* a = stages + s * S::kStageBytes;
         uint8_t* b = a + kABytes;
         mbar_expect_tx(&full[s], S::kStageBytes);
         tma_load_5d(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
@@ -143,10 +147,10 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(kTileM, BLOCK_N, 0, B_MN ? 1 : 0);
       for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % kStages, ph = (kb / kStages) & 1;
+        const int s = kb % nst, ph = (kb / nst) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(smem + s * S::kStageBytes);
+        const uint32_t a_addr = smem_u32(stages + s * S::kStageBytes);
         const uint32_t b_addr = a_addr + kABytes;
         const uint64_t adesc = make_smem_desc(a_addr, 16, 1024);
         const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
@@ -167,7 +171,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     const int row = q * 32 + lane_id();    // tile row == pixel index in the box
     mbar_wait(tmem_full, 0);
     tc_fence_after();
-    uint8_t* stage = smem;                 // pipeline buffers are idle now: reuse as staging
+    uint8_t* stage = stages;               // pipeline buffers are idle now: reuse as staging
 #pragma unroll
     for (int c = 0; c < BLOCK_N / 32; ++c) {
       uint32_t r[32];
@@ -245,6 +249,7 @@ struct WgradParams {
   int ntap_groups;
   int ntaps[4];
   Tap taps[4][9];                 // A(X) coordinate offsets + dW column offset (tap*Cin)
+  int nstages, stage_bytes;       // pipeline depth / bytes per stage (dY tile + the group's tap tiles)
   int Cout, dw_pitch;             // dW row pitch in floats (9*Cin, or 32 for the stem)
   int valid_cols;                 // columns of the ci chunk that exist in dW (stem: 27)
   float* dw;
@@ -255,10 +260,8 @@ struct WgradSmem {
   static constexpr int kDyBytes = 64 * 128 * 2;                   // [64 pix][128 co] as two 64-wide atoms
   static constexpr int kXBytes = 64 * NB * 2;                     // one tap: [64 pix][NB ci]
   static constexpr int kMaxTaps = 512 / NB;                       // TMEM columns
-  static constexpr int kStageBytes = kDyBytes + kMaxTaps * kXBytes;
-  static constexpr int kWStages = (NB == 128) ? 2 : 2;
-  static constexpr int kBarOff = kWStages * kStageBytes;
-  static constexpr int kTotal = kBarOff + 128 + 1024;
+  static constexpr int kBudget = 200 * 1024;                      // stage buffers per CTA
+  static constexpr int total(int nst, int stage_bytes) { return 1024 + kCtrlBytes + nst * stage_bytes; }
 };
 
 template <int NB>
@@ -266,13 +269,14 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
                                                          const __grid_constant__ CUtensorMap tmX,
                                                          const __grid_constant__ WgradParams p) {
   using S = WgradSmem<NB>;
-  constexpr int kWS = S::kWStages;
+  const int kWS = p.nstages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem + S::kBarOff);
-  uint64_t* empty = full + kWS;
-  uint64_t* tmem_full = empty + kWS;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+  uint8_t* stages = smem + kCtrlBytes;
 
   const int warp = threadIdx.x >> 5;
   // blockIdx.y enumerates (co_tile, ci_chunk, tap_group)
@@ -317,7 +321,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
         const int tw = t % p.tiles_w; t /= p.tiles_w;
         const int th = t % p.tiles_h; t /= p.tiles_h;
         const int w0 = tw * p.BW, h0 = th * p.BH, n0 = t * p.BN;
-        uint8_t* dy = smem + s * S::kStageBytes;
+        uint8_t* dy = stages + (size_t)s * p.stage_bytes;
         uint8_t* x = dy + S::kDyBytes;
         mbar_expect_tx(&full[s], stage_tx);
         tma_load_5d(dy, &tmDy, &full[s], cot * 128, w0, 0, h0, n0);
@@ -338,7 +342,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
         const int s = i % kWS, ph = (i / kWS) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t dy_addr = smem_u32(smem + s * S::kStageBytes);
+        const uint32_t dy_addr = smem_u32(stages + (size_t)s * p.stage_bytes);
         const uint32_t x_addr = dy_addr + S::kDyBytes;
         const uint64_t adesc = make_smem_desc(dy_addr, p.co_alias ? 0 : dy_atom_bytes, 1024);
         for (int tp = 0; tp < ntaps; ++tp) {
@@ -356,7 +360,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
     const int q = warp & 3;
     const int lane = lane_id();
     const int et = threadIdx.x - 64;
-    float* stage = reinterpret_cast<float*>(smem);        // [128 co][33] fp32 transpose buffer (16.5 KiB)
+    float* stage = reinterpret_cast<float*>(stages);      // [128 co][33] fp32 transpose buffer (16.5 KiB)
     if (nkb > 0) {
       mbar_wait(tmem_full, 0);
       tc_fence_after();
@@ -491,10 +495,11 @@ static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
   auto kern = tapconv_kernel<BN_, MN_>;
   static bool configured = false;
   if (!configured) {
-    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, ConvSmem<BN_>::kTotal));
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   ConvSmem<BN_>::total(kMaxStages)));
     configured = true;
   }
-  kern<<<pl.grid, kThreads, ConvSmem<BN_>::kTotal, st>>>(pl.tmA, pl.tmB, pl.cp);
+  kern<<<pl.grid, kThreads, ConvSmem<BN_>::total(pl.cp.nstages), st>>>(pl.tmA, pl.tmB, pl.cp);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -504,10 +509,11 @@ static int launch_wgrad(const ConvPlan& pl, cudaStream_t st) {
   auto kern = wgrad_kernel<NB_>;
   static bool configured = false;
   if (!configured) {
-    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, WgradSmem<NB_>::kTotal));
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                   WgradSmem<NB_>::total(1, WgradSmem<NB_>::kBudget)));
     configured = true;
   }
-  kern<<<pl.grid, kThreads, WgradSmem<NB_>::kTotal, st>>>(pl.tmA, pl.tmB, pl.wp);
+  kern<<<pl.grid, kThreads, WgradSmem<NB_>::total(pl.wp.nstages, pl.wp.stage_bytes), st>>>(pl.tmA, pl.tmB, pl.wp);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -538,6 +544,12 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   memset(&pl->cp, 0, sizeof(pl->cp));
   pl->kind = kind;
   pl->block_n = (ngemm % 128 == 0) ? 128 : 64;
+  {
+    // small layers (few pixel tiles): prefer 64-wide N tiles so the grid covers more of the 148 SMs
+    const long long tiles = (long long)N * Ho * Wo / kTileM;
+    const int groups = (kind == 1 && stride == 2 && R == 3) ? 4 : 1;
+    if (pl->block_n == 128 && tiles * (ngemm / 128) * groups < 100) pl->block_n = 64;
+  }
   pl->b_mn = (kind == 1);
   ConvParams& cp = pl->cp;
   cp.red_blocks = red / 64;
@@ -617,6 +629,7 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   }
   if (rc) { delete pl; return rc; }
   pl->grid = dim3(cp.tiles_w * cp.tiles_h * tiles_n, ngemm / pl->block_n, cp.ngroups);
+  cp.nstages = ((long long)pl->grid.x * pl->grid.y * pl->grid.z <= 148) ? kMaxStages : kMinStages;
   *out_plan = pl;
   return 0;
 }
@@ -671,9 +684,17 @@ DPS_API int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int 
   }
   const int total_blocks = wp.tiles_w * wp.tiles_h * wp.tiles_n;
   const int ny = wp.co_tiles * wp.ci_chunks * ngroups;
-  if (nsplit <= 0) nsplit = (148 + ny - 1) / ny;
+  // one CTA per SM (512 TMEM columns each): keep the whole grid inside ONE wave of 148 CTAs
+  if (nsplit <= 0) nsplit = 148 / ny > 0 ? 148 / ny : 1;
   if (nsplit > total_blocks) nsplit = total_blocks;
   wp.nsplit = nsplit;
+  {
+    int max_group = 0;
+    for (int g = 0; g < ngroups; ++g) max_group = wp.ntaps[g] > max_group ? wp.ntaps[g] : max_group;
+    wp.stage_bytes = 64 * 128 * 2 + max_group * 64 * NB * 2;
+    int nst = (200 * 1024) / wp.stage_bytes;
+    wp.nstages = nst > kMaxStages ? kMaxStages : (nst < 2 ? 2 : nst);
+  }
   int rc = make_act_map(&pl->tmA, dy, N, Ho, Wo, Cout, 0, 64, wp.BW, wp.BH, wp.BN);
   if (!rc) rc = make_act_map(&pl->tmB, x, N, H, W, Cin, stride == 2, 64, wp.BW, wp.BH, wp.BN);
   if (rc) { delete pl; return rc; }
@@ -699,7 +720,8 @@ DPS_API int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* sme
   ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
   grid_xyz[0] = pl->grid.x; grid_xyz[1] = pl->grid.y; grid_xyz[2] = pl->grid.z;
   *block_n = pl->block_n;
-  *smem_bytes = pl->kind == 2 ? (pl->block_n == 128 ? WgradSmem<128>::kTotal : WgradSmem<64>::kTotal)
-                              : (pl->block_n == 128 ? ConvSmem<128>::kTotal : ConvSmem<64>::kTotal);
+  *smem_bytes = pl->kind == 2 ? WgradSmem<64>::total(pl->wp.nstages, pl->wp.stage_bytes)
+                              : (pl->block_n == 128 ? ConvSmem<128>::total(pl->cp.nstages)
+                                                    : ConvSmem<64>::total(pl->cp.nstages));
   return 0;
 }

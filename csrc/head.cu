@@ -104,34 +104,51 @@ __global__ void __launch_bounds__(kHeadThreads) head_sample_kernel(
   }
 }
 
-__global__ void __launch_bounds__(kHeadThreads) head_param_kernel(
+// grid = (K classes, F / 128 feature chunks), 128 threads: one (class, feature) pair per thread.
+__global__ void __launch_bounds__(128) head_param_kernel(
     const float* __restrict__ pooled, const float* __restrict__ dlogits, const float* __restrict__ loss_n,
     const int* __restrict__ correct_n, float* __restrict__ dw, float* __restrict__ db, float* __restrict__ out,
     int N, int F, int K, int training) {
+  __shared__ float s_dl[1024];
   const int j = blockIdx.x;
   const int tid = threadIdx.x;
   if (training && j < K) {
-    for (int c = tid; c < F; c += blockDim.x) {
-      float s = 0.f;
-      for (int n = 0; n < N; ++n) s += dlogits[(size_t)n * kMaxClasses + j] * pooled[(size_t)n * F + c];
-      dw[(size_t)j * F + c] += s;
-    }
-    if (tid < 32) {
-      float s = 0.f;
-      for (int n = tid; n < N; n += 32) s += dlogits[(size_t)n * kMaxClasses + j];
-      s = warp_sum(s);
-      if (tid == 0) db[j] += s;
+    for (int n0 = 0; n0 < N; n0 += 1024) {
+      const int cnt = min(1024, N - n0);
+      __syncthreads();
+      for (int n = tid; n < cnt; n += blockDim.x) s_dl[n] = dlogits[(size_t)(n0 + n) * kMaxClasses + j];
+      __syncthreads();
+      const int c = blockIdx.y * 128 + tid;
+      if (c < F) {
+        float acc = 0.f;
+        int n = 0;
+        for (; n + 8 <= cnt; n += 8) {
+          float v[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) v[u] = pooled[(size_t)(n0 + n + u) * F + c];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) acc += s_dl[n + u] * v[u];
+        }
+        for (; n < cnt; ++n) acc += s_dl[n] * pooled[(size_t)(n0 + n) * F + c];
+        dw[(size_t)j * F + c] += acc;
+      }
+      if (blockIdx.y == 0 && tid < 32) {
+        float sdl = 0.f;
+        for (int n = tid; n < cnt; n += 32) sdl += s_dl[n];
+        sdl = warp_sum(sdl);
+        if (tid == 0) db[j] += sdl;
+      }
     }
   }
-  if (j == 0 && tid >= 32 && tid < 64) {
+  if (j == 0 && blockIdx.y == 0 && tid >= 32 && tid < 64) {
     const int lane = tid - 32;
-    float s = 0.f;
+    float sl = 0.f;
     int c = 0;
-    for (int n = lane; n < N; n += 32) { s += loss_n[n]; c += correct_n[n]; }
-    s = warp_sum(s);
+    for (int n = lane; n < N; n += 32) { sl += loss_n[n]; c += correct_n[n]; }
+    sl = warp_sum(sl);
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) c += __shfl_xor_sync(0xffffffffu, c, o);
-    if (lane == 0) { out[0] = s / (float)N; out[1] = (float)c; }
+    if (lane == 0) { out[0] = sl / (float)N; out[1] = (float)c; }
   }
 }
 
@@ -179,8 +196,8 @@ DPS_API int dps_head_forward_backward(const void* act, const void* w, const floa
                                                  pooled, dlogits, loss_n, correct_n, (__nv_bfloat16*)d_act, N, HW, F,
                                                  K, training);
   DPS_CHECK(cudaGetLastError());
-  head_param_kernel<<<training ? K : 1, kHeadThreads, 0, st>>>(pooled, dlogits, loss_n, correct_n, dw, db, out, N, F,
-                                                               K, training);
+  head_param_kernel<<<dim3(training ? K : 1, training ? (F + 127) / 128 : 1), 128, 0, st>>>(
+      pooled, dlogits, loss_n, correct_n, dw, db, out, N, F, K, training);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

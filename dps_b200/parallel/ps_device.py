@@ -27,9 +27,10 @@ from .fabric import ArenaSpec, Fabric
 
 
 def _default_ctas(shard_elems: int) -> int:
-    # every CTA must be co-resident (owner CTAs spin on arrival counters): stay <= 1 CTA / SM
-    want = max(8, shard_elems // (256 * 8 * 4))
-    return int(min(128, want))
+    # every CTA must be co-resident (owner CTAs spin on arrival counters).  256-thread CTAs with no shared
+    # memory fit 8 per SM, so 4 per SM (592) is always resident and gives the copy loops enough loads in flight.
+    want = max(8, shard_elems // (256 * 8 * 2))
+    return int(min(592, want))
 
 
 class DevicePS:
