@@ -36,7 +36,7 @@ __device__ __forceinline__ uint4 pack8(const V8& r) {
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
-    const __nv_bfloat16* __restrict__ x, const double* __restrict__ stats, const float* __restrict__ gamma,
+    const __nv_bfloat16* __restrict__ x, const long long* __restrict__ stats, const float* __restrict__ gamma,
     const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
     float* __restrict__ save_mean, float* __restrict__ save_rstd, float* __restrict__ running_mean,
     float* __restrict__ running_var, long long* __restrict__ num_batches, long long P, int C, int relu,
@@ -45,9 +45,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var;
     if (training) {
-      const double m = stats[c] / (double)P;
+      // 64-bit fixed point from the conv epilogue: sum x 2^32, sum of squares x 2^24
+      const double m = (double)stats[c] * (1.0 / 4294967296.0) / (double)P;
       mean = (float)m;
-      var = fmaxf((float)(stats[C + c] / (double)P - m * m), 0.f);
+      var = fmaxf((float)((double)stats[C + c] * (1.0 / 16777216.0) / (double)P - m * m), 0.f);
     } else {
       mean = running_mean[c];
       var = running_var[c];
@@ -226,7 +227,7 @@ static int bn_grid(long long nvec) {
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 
-DPS_API int dps_bn_forward(const void* x, const double* stats, const float* gamma, const float* beta,
+DPS_API int dps_bn_forward(const void* x, const long long* stats, const float* gamma, const float* beta,
                            const void* residual, void* y, float* save_mean, float* save_rstd, float* running_mean,
                            float* running_var, long long* num_batches, long long P, int C, int relu, int training,
                            float eps, float momentum, void* stream) {

@@ -36,11 +36,13 @@ namespace dps {
 
 constexpr int kMinStages = 3;      // 2 CTAs / SM when the grid has several waves
 constexpr int kMaxStages = 6;      // 1 CTA / SM (grid <= one wave): deeper pipeline hides the L2->smem latency
-constexpr int kCtrlBytes = 1024;   // barriers + TMEM slot live in front of the stage buffers
+constexpr int kCtrlBytes = 128;    // barriers + TMEM slot, placed right after the stage buffers
 constexpr int kTileM = 128;         // pixels per CTA tile == UMMA M
 constexpr int kKBlock = 64;         // reduction elements per pipeline stage (one 128-byte swizzle row)
 constexpr int kABytes = kTileM * kKBlock * 2;   // 16 KiB
 constexpr int kThreads = 192;
+constexpr double kStatSumScale = 4294967296.0;   // 2^32  (keep in sync with bn.cu)
+constexpr double kStatSqScale = 16777216.0;      // 2^24
 
 struct Tap {
   int16_t c_off;   // added to the A channel coordinate (parity view: pw*C)
@@ -63,8 +65,9 @@ struct ConvParams {
   int out_H, out_W, out_C;        // output tensor dims (pixels are written at (h*os+oph, w*os+opw))
   __nv_bfloat16* out;
   const __nv_bfloat16* addend;    // optional, same shape as out
-  double* stats;                  // optional [2*out_C]: per-channel sum, sum of squares (fp64 atomics:
-                                  // order-independent to ~1e-16, so BN statistics are run-to-run stable)
+  long long* stats;               // optional [2*out_C]: per-channel sum (x 2^32) and sum of squares (x 2^24) in
+                                  // 64-bit fixed point: integer atomics are exact and order-independent, so
+                                  // BN statistics are bit-identical run to run (and full-rate in L2)
 };
 
 template <int BLOCK_N>
@@ -72,7 +75,7 @@ struct ConvSmem {
   static constexpr int kBBytes = BLOCK_N * kKBlock * 2;
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPitch = BLOCK_N * 2 + 16;                 // staging row pitch (bank-conflict free)
-  static constexpr int total(int nst) { return 1024 + kCtrlBytes + nst * kStageBytes; }   // 1024 = alignment slack
+  static constexpr int total(int nst) { return 1024 + nst * kStageBytes + kCtrlBytes; }   // 1024 = alignment slack
   static_assert(kTileM * kPitch <= kMinStages * kStageBytes, "staging must fit in the pipeline buffers");
 };
 
@@ -83,12 +86,12 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   using S = ConvSmem<BLOCK_N>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  const int nst = p.nstages;
+  uint8_t* stages = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + nst * S::kStageBytes);
   uint64_t* empty = full + kMaxStages;
   uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  uint8_t* stages = smem + kCtrlBytes;
-  const int nst = p.nstages;
 
   const int warp = threadIdx.x >> 5;
   const int grp = blockIdx.z;
@@ -201,8 +204,10 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
         s += v;
         ss += v * v;
       }
-      atomicAdd(p.stats + c_out0 + ch, (double)s);
-      atomicAdd(p.stats + p.out_C + c_out0 + ch, (double)ss);
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + c_out0 + ch),
+                (unsigned long long)__double2ll_rn((double)s * kStatSumScale));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + p.out_C + c_out0 + ch),
+                (unsigned long long)__double2ll_rn((double)ss * kStatSqScale));
     }
 
     constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
@@ -261,7 +266,7 @@ struct WgradSmem {
   static constexpr int kXBytes = 64 * NB * 2;                     // one tap: [64 pix][NB ci]
   static constexpr int kMaxTaps = 512 / NB;                       // TMEM columns
   static constexpr int kBudget = 200 * 1024;                      // stage buffers per CTA
-  static constexpr int total(int nst, int stage_bytes) { return 1024 + kCtrlBytes + nst * stage_bytes; }
+  static constexpr int total(int nst, int stage_bytes) { return 1024 + nst * stage_bytes + kCtrlBytes; }
 };
 
 template <int NB>
@@ -272,11 +277,11 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
   const int kWS = p.nstages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
-  uint64_t* full = reinterpret_cast<uint64_t*>(smem);
+  uint8_t* stages = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + (size_t)kWS * p.stage_bytes);
   uint64_t* empty = full + kMaxStages;
   uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
-  uint8_t* stages = smem + kCtrlBytes;
 
   const int warp = threadIdx.x >> 5;
   // blockIdx.y enumerates (co_tile, ci_chunk, tap_group)
@@ -528,7 +533,7 @@ using namespace dps;
 // fprop:  x [N][H][W][Cin] -> out [N][H/stride][W/stride][Cout];  w [Cout][R*R*Cin] (row pitch w_pitch)
 // dgrad:  x is dY [N][H/stride][W/stride][Cout] -> out dX [N][H][W][Cin] (H, W are ALWAYS the conv input dims)
 DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, const void* addend,
-                                 double* stats, int N, int H, int W, int Cin, int Cout, int R, int stride,
+                                 long long* stats, int N, int H, int W, int Cin, int Cout, int R, int stride,
                                  int w_cols, int w_pitch, void** out_plan) {
   if (kind != 0 && kind != 1) DPS_FAIL(1, "kind must be 0 (fprop) or 1 (dgrad)");
   if (R != 1 && R != 3) DPS_FAIL(1, "R must be 1 or 3");

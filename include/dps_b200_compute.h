@@ -18,7 +18,7 @@ extern "C" {
  * kind 1 = dgrad : x = dY[N][H/s][W/s][Cout]       -> out = dX[N][H][W][Cin] (+ addend, may alias out)
  * w is [Cout][w_pitch] bf16 with w_cols valid columns ordered (r, s, ci).  H, W are the conv INPUT dims.
  * Plans own their TMA descriptors; buffers must stay at the same addresses for the plan's lifetime. */
-int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, const void* addend, double* stats,
+int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, const void* addend, long long* stats,
                          int N, int H, int W, int Cin, int Cout, int R, int stride, int w_cols, int w_pitch,
                          void** out_plan);
 /* wgrad: dw[Cout][dw_pitch] fp32 += dY^T * im2col(x)   (atomic accumulation: the caller zeroes dw) */
@@ -29,9 +29,9 @@ int dps_conv_plan_destroy(void* plan);
 int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* smem_bytes);
 
 /* ---- fused BatchNorm(+residual)+ReLU (reference: nn.BatchNorm2d + torch.relu + `out += shortcut(x)`,
- *      server.py:25-40,49,67-68).  x, residual, y: [P][C] bf16 (NHWC flattened); stats = [2C] fp64 sum / sumsq
- *      produced by the conv epilogue.  training == 0 normalises with the running statistics. ---- */
-int dps_bn_forward(const void* x, const double* stats, const float* gamma, const float* beta, const void* residual,
+ *      server.py:25-40,49,67-68).  x, residual, y: [P][C] bf16 (NHWC flattened); stats = [2C] 64-bit fixed-point
+ *      sum (x2^32) / sumsq (x2^24) produced by the conv epilogue.  training == 0 normalises with the running statistics. ---- */
+int dps_bn_forward(const void* x, const long long* stats, const float* gamma, const float* beta, const void* residual,
                    void* y, float* save_mean, float* save_rstd, float* running_mean, float* running_var,
                    long long* num_batches, long long P, int C, int relu, int training, float eps, float momentum,
                    void* stream);

@@ -52,14 +52,14 @@ def test_fprop(shape):
     x, w, dy = _mk(*shape)
     y_ref, _, _ = _ref(x, w, dy, R, stride)
     out = torch.zeros(N, H // stride, H // stride, Cout, device="cuda", dtype=torch.bfloat16)
-    stats = torch.zeros(2 * Cout, device="cuda", dtype=torch.float64)
+    stats = torch.zeros(2 * Cout, device="cuda", dtype=torch.int64)     # fixed point: sum x2^32, sumsq x2^24
     ConvPlan.fprop(x, w, out, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride, stats=stats).run()
     torch.cuda.synchronize()
     assert _relerr(out, y_ref) < 1.5e-2, _relerr(out, y_ref)
     # fused BN statistics are taken over the stored bf16 values
     of = out.float().reshape(-1, Cout)
-    assert torch.allclose(stats[:Cout].float(), of.sum(0), rtol=2e-3, atol=2e-1)
-    assert torch.allclose(stats[Cout:].float(), (of * of).sum(0), rtol=2e-3, atol=2e-1)
+    assert torch.allclose((stats[:Cout].double() / 2 ** 32).float(), of.sum(0), rtol=2e-3, atol=2e-1)
+    assert torch.allclose((stats[Cout:].double() / 2 ** 24).float(), (of * of).sum(0), rtol=2e-3, atol=2e-1)
 
 
 @pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
