@@ -109,13 +109,18 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
         F8 z = {};                                            // gradients are consumed: zero for next step
         store_f32x8(grad + g, z);
       }
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        __threadfence_system();
-        red_release_sys_add(T.flags[o] + DPS_F_ARRIVE + r, 1u);
-        if (b == 0) st_release_sys(T.flags[o] + DPS_F_HEARTBEAT + r, step + 1);
+    }
+    // one system-scope fence for all W destinations, then relaxed arrivals (a release per owner would cost a
+    // MEMBAR.SYS each): every store above happens-before the fence through the CTA barrier
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      __threadfence_system();
+      for (int o = 0; o < W; ++o) {
+        red_relaxed_sys_add(T.flags[o] + DPS_F_ARRIVE + r, 1u);
+        if (b == 0) st_relaxed_sys(T.flags[o] + DPS_F_HEARTBEAT + r, step + 1);
       }
     }
+    __syncthreads();
   }
 
   // ---- phase B: owners wait for all sources, reduce and update
@@ -168,7 +173,7 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
       store_f32x8(master + l, p);
     }
     __syncthreads();
-    if (threadIdx.x == 0 && b == 0) T.flags[o][DPS_F_VERSION] = step + 1;
+    if (threadIdx.x == 0 && b == 0) T.flags[o][DPS_F_VERSION] += 1;   // shard version (survives checkpoint resume)
   }
 }
 
@@ -198,8 +203,8 @@ __global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__
     }
     __syncthreads();
     if (threadIdx.x == 0) {
-      __threadfence_system();
-      for (int w = 0; w < W; ++w) red_release_sys_add(T.flags[w] + DPS_F_PULLCOUNT, 1u);
+      __threadfence_system();                                  // one fence, then relaxed signals to all workers
+      for (int w = 0; w < W; ++w) red_relaxed_sys_add(T.flags[w] + DPS_F_PULLCOUNT, 1u);
     }
   }
 }

@@ -51,11 +51,11 @@ class DevicePS:
         spec.add("flags", L.FLAG_WORDS * 4)
         spec.add("stage", world * self.E * (2 if self.compress else 4))
         spec.add("wbf16", self.total * 2)
-        spec.add("small", self.n_small * 4)
+        spec.add("small", max(self.n_small, 8) * 4)
         if self.is_async:
             spec.add("ring", self.R * self.E * 2)
             spec.add("pub", self.E * 2)
-            spec.add("pubsmall", self.n_small * 4)
+            spec.add("pubsmall", max(self.n_small, 8) * 4)
         self.fabric = Fabric(rank, world, device_index, spec, emulate=emulate, group=group)
         self.lib = self.fabric.lib
 

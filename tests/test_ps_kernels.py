@@ -160,3 +160,72 @@ def test_async_ring_staleness_and_rejection():
     assert torch.equal(ps.wbf16[2], got.to(torch.bfloat16))
     assert ps.error_bits(0) == 0
     ps.close()
+
+
+def test_barrier_timeout_drops_dead_rank_and_flags_it():
+    """SURVEY Q3 / §5.3 fault injection: rank 2 of 3 never pushes.  Owners do not hang: after the bounded
+    wait they average over the ranks present, record the missing rank and raise the sticky error bit."""
+    from dps_b200.ops import _lib as L
+    from dps_b200.parallel.watchdog import decode_error_bits, missing_ranks
+    W = 3
+    model, layout, ps, flat0 = _setup(W, mode="sync", lr=0.1)
+    ps.timeout_ns = int(0.2e9)
+    ps.tables.rank_hi = 2                                     # ranks 0 and 1 are alive; rank 2 is dead
+    gs = [torch.randn(layout.total, device="cuda", generator=torch.Generator("cuda").manual_seed(r)) * 0.05
+          for r in range(2)]
+    for r in range(2):
+        ps.grad[r].copy_(gs[r])
+    ps.push_sync()
+    torch.cuda.synchronize()
+    want = flat0 - 0.1 * (gs[0].half().float() + gs[1].half().float()) / 2
+    got = ps.gather_master()
+    sh_want, sh_got = layout.to_shards(want), layout.to_shards(got)
+    for o in range(2):
+        assert torch.allclose(sh_got[o], sh_want[o], rtol=1e-5, atol=1e-6)
+        assert decode_error_bits(ps.error_bits(o)) == ["barrier_timeout"]
+        assert missing_ranks(int(ps.flag_words(o)[L.F_MISSING]) & 0xFFFFFFFF, W) == [2]
+    assert torch.equal(sh_got[2], layout.to_shards(flat0)[2])          # the dead rank's shard is untouched
+    ps.close()
+
+
+def test_heartbeat_watchdog_logic():
+    from dps_b200.parallel.watchdog import HeartbeatWatchdog
+    hb, now = [0, 0, 0], [0.0]
+    wd = HeartbeatWatchdog(lambda: hb, 3, timeout_s=5.0, clock=lambda: now[0])
+    assert wd.poll() == []
+    for t in range(1, 8):
+        now[0] = float(t)
+        hb[0] += 1
+        hb[1] += 1                                            # rank 2 never advances
+        stale = wd.poll()
+    assert stale == [2]
+
+
+def test_checkpoint_resume_through_job(tmp_path):
+    """W16: save from the sharded store, load into the reference-shaped torch module, resume a new Job."""
+    from dps_b200 import Config
+    from dps_b200.api import Job
+    from dps_b200.models.resnet import ResNet18
+    cfg = Config(mode="sync", workers=1, batch_size=16, lr=0.05, momentum=0.9)
+    job = Job(cfg, rank=0, world=1, device_index=0)
+    g = torch.Generator().manual_seed(0)
+    x, y = torch.randn(16, 3, 32, 32, generator=g), torch.randint(0, 100, (16,), generator=g)
+    for _ in range(3):
+        job.worker.train_step(x, y).item()
+    path = str(tmp_path / "ck.pt")
+    job.server.save_checkpoint(path)
+    sd = job.server.state_dict()
+    mom = job.ps.gather_momentum().clone()
+    job.close()
+    m = ResNet18(100)
+    m.load_state_dict(torch.load(path, weights_only=True), strict=True)        # reference-compatible file
+    assert torch.equal(m.fc.weight, sd["fc.weight"])
+    job2 = Job(cfg.replace(resume=path), rank=0, world=1, device_index=0)
+    assert job2.server.global_step == 3
+    sd2 = job2.server.state_dict()
+    for k in ("conv1.weight", "layer3.0.shortcut.0.weight", "fc.bias", "bn1.running_var"):
+        assert torch.allclose(sd2[k], sd[k]), k
+    assert torch.allclose(job2.ps.gather_momentum(), mom)
+    l = job2.worker.train_step(x, y).item()
+    assert l == l and job2.server.global_step == 4
+    job2.close()
