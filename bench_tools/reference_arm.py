@@ -43,7 +43,8 @@ def run_reference(args) -> dict:
         return {"impl": "reference", "unavailable": f"reference dependency missing: {e}"}
     N, K, W, B = args.gpus, args.steps, args.warmup, args.batch
     epochs = 2 if W > 0 else 1
-    steps_per_epoch = max(K, W)
+    # the reference needs seconds per step (CPU + pickle over gRPC): cap the timed epoch so the arm finishes
+    steps_per_epoch = min(max(K, W), 10 if N >= 4 else 20)
     train_samples = N * B * steps_per_epoch
     port = _free_port()
     launch = os.path.join(ROOT, "bench_tools", "ref_launch.py")
