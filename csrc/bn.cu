@@ -17,6 +17,7 @@ namespace dps {
 
 constexpr int kBnThreads = 256;
 constexpr int kMaxC = 512;
+constexpr double kGradSumScale = 1099511627776.0;   // 2^40 (keep in sync with conv_tc.cu)
 
 struct V8 {
   float v[8];
@@ -108,10 +109,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
     const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ y, const __nv_bfloat16* __restrict__ x,
     const float* __restrict__ mean, const float* __restrict__ rstd, __nv_bfloat16* __restrict__ dz,
-    double* __restrict__ sums, long long P, int C, int relu) {
-  // Cross-thread reduction in a fixed order (no shared-memory atomics), then ONE fp64 global atomic per channel
-  // per CTA: the result is independent of atomic ordering to ~1e-16, so the activation gradients of a step are
-  // reproducible run to run (bf16 re-rounding would otherwise amplify fp32 summation jitter).
+    long long* __restrict__ sums, long long P, int C, int relu) {
+  // Cross-thread reduction in a fixed order (no shared-memory atomics), then ONE 64-bit fixed-point (x 2^40)
+  // integer atomic per channel per CTA: integer adds are exact and order-independent, so the activation gradients
+  // of a step are bit-reproducible run to run (bf16 re-rounding would otherwise amplify fp32 summation jitter).
   __shared__ float s_part[kBnThreads * 16];            // [row slot][2C] partials
   const int cg = C / 8;                               // channel groups; 256 % cg == 0
   const int my_cg = threadIdx.x % cg;
@@ -164,18 +165,20 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
   for (int c = threadIdx.x; c < 2 * C; c += blockDim.x) {
     double acc = 0.0;
     for (int k = 0; k < rows_per_pass; ++k) acc += (double)s_part[k * 2 * C + c];
-    atomicAdd(sums + c, acc);
+    atomicAdd(reinterpret_cast<unsigned long long*>(sums + c),
+              (unsigned long long)__double2ll_rn(acc * kGradSumScale));
   }
 }
 
 __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean,
-    const float* __restrict__ rstd, const float* __restrict__ gamma, const double* __restrict__ sums,
+    const float* __restrict__ rstd, const float* __restrict__ gamma, const long long* __restrict__ sums,
     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, long long P, int C) {
   __shared__ float s_a[kMaxC], s_b[kMaxC], s_c[kMaxC];   // dx = s_a*dz + s_b*x + s_c
   const float invP = 1.f / (float)P;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float sdz = (float)sums[c], sdzx = (float)sums[C + c];
+    const float sdz = (float)((double)sums[c] * (1.0 / kGradSumScale));
+    const float sdzx = (float)((double)sums[C + c] * (1.0 / kGradSumScale));
     const float gr = gamma[c] * rstd[c];
     // dx = gr * (dz - sdz/P - xhat * sdzx/P),  xhat = (x - mean) * rstd
     const float k = gr * rstd[c] * sdzx * invP;
@@ -239,10 +242,10 @@ DPS_API int dps_bn_forward(const void* x, const long long* stats, const float* g
   return 0;
 }
 
-// sums must be zero on entry ([2*C] fp32).  dz may alias dy.  When relu == 0, dz is not written and the
+// sums must be zero on entry ([2*C] int64, fixed point x 2^40).  dz may alias dy.  When relu == 0, dz is not written and the
 // apply pass should be given dy.
 DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
-                            const float* gamma, void* dz, double* sums, void* dx, float* dgamma, float* dbeta,
+                            const float* gamma, void* dz, long long* sums, void* dx, float* dgamma, float* dbeta,
                             long long P, int C, int relu, void* stream) {
   if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
   const int rows_per_pass = kBnThreads / (C / 8);
@@ -259,15 +262,26 @@ DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const 
   return 0;
 }
 
+DPS_API int dps_bn_backward_apply(const void* dz, const void* x, const float* mean, const float* rstd,
+                                  const float* gamma, const long long* sums, void* dx, float* dgamma, float* dbeta,
+                                  long long P, int C, void* stream) {
+  if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
+  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dz, (const __nv_bfloat16*)x, mean, rstd, gamma, sums, (__nv_bfloat16*)dx, dgamma, dbeta,
+      P, C);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------------
 // BatchNorm backward for callers that must not allocate.
 //
-// dps_bn_backward() needs a [2*C] fp64 reduction scratch from its caller.  Some callers have nowhere to
+// dps_bn_backward() needs a [2*C] 64-bit reduction scratch from its caller.  Some callers have nowhere to
 // get one: a serving or training process whose device memory was handed in full to a pool with a hard
 // budget at start-up (a later cudaMalloc fails or is forbidden by policy), a latency-critical loop where the
 // implicit device-wide synchronisation of cudaMalloc/cudaFree is not acceptable, or a hook / plug-in callback
 // that only receives its input and output buffers.  For them the scratch lives inside the library image:
-// one file-scope __device__ array of kNoAllocMaxC = 512 channels (2 * 512 doubles = 8 KiB), resident on every
+// one file-scope __device__ array of kNoAllocMaxC = 512 channels (2 * 512 64-bit words = 8 KiB), resident on every
 // GPU that loads the library until the process exits.
 //
 // Rules that follow from sharing one array:
@@ -285,14 +299,14 @@ DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const 
 namespace dps {
 constexpr int kNoAllocMaxC = 512;
 constexpr int kNoAllocMaxDevices = 64;
-static __device__ __align__(256) double g_bn_noalloc_scratch[2 * kNoAllocMaxC];
+static __device__ __align__(256) long long g_bn_noalloc_scratch[2 * kNoAllocMaxC];
 }  // namespace dps
 
 #include <mutex>
 
-static int bn_noalloc_scratch_ptr(double** out) {
+static int bn_noalloc_scratch_ptr(long long** out) {
   static std::mutex mu;
-  static double* resolved[kNoAllocMaxDevices] = {nullptr};
+  static long long* resolved[kNoAllocMaxDevices] = {nullptr};
   int dev = -1;
   DPS_CHECK(cudaGetDevice(&dev));
   if (dev < 0 || dev >= kNoAllocMaxDevices) DPS_FAIL(1, "bn_backward_noalloc: device index %d not supported", dev);
@@ -302,7 +316,7 @@ static int bn_noalloc_scratch_ptr(double** out) {
     // once per device, with that device current: the symbol has a different address on every GPU
     DPS_CHECK(cudaGetSymbolAddress(&p, g_bn_noalloc_scratch));
     if (p == nullptr) DPS_FAIL(1, "bn_backward_noalloc: cudaGetSymbolAddress returned a null address");
-    resolved[dev] = static_cast<double*>(p);
+    resolved[dev] = static_cast<long long*>(p);
   }
   *out = resolved[dev];
   return 0;
@@ -315,14 +329,14 @@ DPS_API int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x
                                     float* dbeta, long long P, int C, int relu, void* stream) {
   if (C > kNoAllocMaxC)
     DPS_FAIL(1, "bn_backward_noalloc: C=%d exceeds the built-in scratch (max %d channels); use dps_bn_backward "
-                "with a caller-provided [2*C] fp64 buffer", C, kNoAllocMaxC);
+                "with a caller-provided [2*C] int64 buffer", C, kNoAllocMaxC);
   if (C <= 0 || C % 8 || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
   if (P <= 0) DPS_FAIL(1, "bn_backward_noalloc: P must be positive");
-  double* sums = nullptr;
+  long long* sums = nullptr;
   if (int e = bn_noalloc_scratch_ptr(&sums)) return e;
   cudaStream_t st = (cudaStream_t)stream;
   // the shared array still holds the previous call's sums: clear exactly what this call accumulates into
-  DPS_CHECK(cudaMemsetAsync(sums, 0, sizeof(double) * 2 * (size_t)C, st));
+  DPS_CHECK(cudaMemsetAsync(sums, 0, sizeof(long long) * 2 * (size_t)C, st));
   const int rows_per_pass = kBnThreads / (C / 8);
   long long want = (P + rows_per_pass - 1) / rows_per_pass;
   const int g1 = (int)(want < 148 * 4 ? (want < 1 ? 1 : want) : 148 * 4);

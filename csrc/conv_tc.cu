@@ -43,6 +43,7 @@ constexpr int kABytes = kTileM * kKBlock * 2;   // 16 KiB
 constexpr int kThreads = 192;
 constexpr double kStatSumScale = 4294967296.0;   // 2^32  (keep in sync with bn.cu)
 constexpr double kStatSqScale = 16777216.0;      // 2^24
+constexpr double kGradSumScale = 1099511627776.0;  // 2^40: BN-backward sums (keep in sync with bn.cu)
 
 struct Tap {
   int16_t c_off;   // added to the A channel coordinate (parity view: pw*C)
@@ -65,6 +66,15 @@ struct ConvParams {
   int out_H, out_W, out_C;        // output tensor dims (pixels are written at (h*os+oph, w*os+opw))
   __nv_bfloat16* out;
   const __nv_bfloat16* addend;    // optional, same shape as out
+  // optional fusion of the NEXT BatchNorm's backward reduction into this (dgrad) epilogue: the tile just computed
+  // is dy of that BN; with its forward output y (ReLU mask) and input x the epilogue stores dz = dy * (y > 0)
+  // and accumulates sum(dz), sum(dz * xhat) per channel (64-bit fixed point x 2^40) -- bn_bwd_reduce disappears.
+  const __nv_bfloat16* fuse_y;
+  const __nv_bfloat16* fuse_x;
+  const float* fuse_mean;
+  const float* fuse_rstd;
+  long long* fuse_sums;
+  int addend_compact;             // addend is indexed at tile resolution (stride-2 dgrad + 1x1 shortcut gradient)
   long long* stats;               // optional [2*out_C]: per-channel sum (x 2^32) and sum of squares (x 2^24) in
                                   // 64-bit fixed point: integer atomics are exact and order-independent, so
                                   // BN statistics are bit-identical run to run (and full-rate in L2)
@@ -76,7 +86,7 @@ struct ConvSmem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPitch = BLOCK_N * 2 + 16;                 // staging row pitch (bank-conflict free)
   static constexpr int total(int nst) { return 1024 + nst * kStageBytes + kCtrlBytes; }   // 1024 = alignment slack
-  static_assert(kTileM * kPitch <= kMinStages * kStageBytes, "staging must fit in the pipeline buffers");
+  static_assert(2 * kTileM * kPitch <= kMinStages * kStageBytes, "two staging tiles must fit in the pipeline buffers");
 };
 
 template <int BLOCK_N, bool B_MN>
@@ -172,9 +182,47 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     // ===================== epilogue (4 warps) =====================
     const int q = warp & 3;                // TMEM lane quadrant this warp may access
     const int row = q * 32 + lane_id();    // tile row == pixel index in the box
+    // Epilogue-side operands that do not depend on the accumulator (residual-gradient addend, and y / x of the BN
+    // whose backward reduction is fused here) are fetched in groups of kGroup rows with all loads of a group in
+    // flight at once; the first group is issued BEFORE waiting for the MMAs, so its latency hides under the mainloop.
+    constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
+    constexpr int kRowsPerPass = 128 / kChunks;
+    constexpr int kPasses = kTileM / kRowsPerPass;        // 8 (N=64) or 16 (N=128)
+    constexpr int kGroup = 4;
+    const int et = threadIdx.x - 64;                      // 0..127
+    const int chunk = et % kChunks, row0 = et / kChunks;
+    const int boxhw = p.BW * p.BH;
+    const bool fuse = p.fuse_y != nullptr;
+    const bool use_addend = p.addend != nullptr && (!p.addend_compact || (p.oph[grp] == 0 && p.opw[grp] == 0));
+    auto out_off = [&](int rr) -> size_t {
+      const int n = n0 + rr / boxhw, rem = rr % boxhw;
+      const int oh = (h0 + rem / p.BW) * p.os + p.oph[grp], ow = (w0 + rem % p.BW) * p.os + p.opw[grp];
+      return (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
+    };
+    auto addend_off = [&](int rr) -> size_t {
+      if (!p.addend_compact) return out_off(rr);
+      const int n = n0 + rr / boxhw, rem = rr % boxhw;
+      return (((size_t)n * (p.out_H / p.os) + h0 + rem / p.BW) * (p.out_W / p.os) + w0 + rem % p.BW) * p.out_C +
+             c_out0 + chunk * 8;
+    };
+    uint4 aa[kGroup], ya[kGroup], xa[kGroup];
+    auto issue = [&](int g) {
+#pragma unroll
+      for (int j = 0; j < kGroup; ++j) {
+        const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+        if (use_addend) aa[j] = ld_nc_v4(p.addend + addend_off(rr));
+        if (fuse) {
+          const size_t off = out_off(rr);
+          ya[j] = ld_nc_v4(p.fuse_y + off);
+          xa[j] = ld_nc_v4(p.fuse_x + off);
+        }
+      }
+    };
+    if (use_addend || fuse) issue(0);
     mbar_wait(tmem_full, 0);
     tc_fence_after();
     uint8_t* stage = stages;               // pipeline buffers are idle now: reuse as staging
+    uint8_t* stage_x = stage + kTileM * S::kPitch;        // second staging tile (x of the fused BN)
 #pragma unroll
     for (int c = 0; c < BLOCK_N / 32; ++c) {
       uint32_t r[32];
@@ -191,8 +239,6 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     }
     tc_fence_before();
     asm volatile("bar.sync 1, 128;" ::: "memory");      // epilogue warps only
-    const int et = threadIdx.x - 64;                      // 0..127
-
     if (p.stats != nullptr) {
       // fused BatchNorm statistics over the bf16 values that are actually stored
       constexpr int kHalves = 128 / BLOCK_N;              // 2 for N=64, 1 for N=128
@@ -210,26 +256,53 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
                 (unsigned long long)__double2ll_rn((double)ss * kStatSqScale));
     }
 
-    constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
-    constexpr int kRowsPerPass = 128 / kChunks;
-    const int chunk = et % kChunks;
-    const int boxhw = p.BW * p.BH;
-    for (int rr = et / kChunks; rr < kTileM; rr += kRowsPerPass) {
-      const int n = n0 + rr / boxhw;
-      const int rem = rr % boxhw;
-      const int oh = (h0 + rem / p.BW) * p.os + p.oph[grp];
-      const int ow = (w0 + rem % p.BW) * p.os + p.opw[grp];
-      const size_t off = (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
-      uint4 v = *reinterpret_cast<const uint4*>(stage + rr * S::kPitch + chunk * 16);
-      if (p.addend != nullptr) {
-        const uint4 a = ld_v4(p.addend + off);
-        float2 x, y;
-        x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
-        x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
-        x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
-        x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
+    for (int g = 0; g < kPasses / kGroup; ++g) {
+      if (g > 0) issue(g);
+#pragma unroll
+      for (int j = 0; j < kGroup; ++j) {
+        const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+        const size_t off = out_off(rr);
+        uint4 v = *reinterpret_cast<const uint4*>(stage + rr * S::kPitch + chunk * 16);
+        if (use_addend) {
+          const uint4 a = aa[j];
+          float2 x, y;
+          x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
+          x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
+          x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
+          x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
+        }
+        if (fuse) {
+          const uint4 yv = ya[j];
+          // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
+          auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
+            const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
+            const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
+            return gg & (lo | hi);
+          };
+          v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
+          *reinterpret_cast<uint4*>(stage + rr * S::kPitch + chunk * 16) = v;       // dz, for the reduction below
+          *reinterpret_cast<uint4*>(stage_x + rr * S::kPitch + chunk * 16) = xa[j];
+        }
+        st_v4(p.out + off, v);
       }
-      st_v4(p.out + off, v);
+    }
+    if (fuse) {
+      asm volatile("bar.sync 1, 128;" ::: "memory");
+      constexpr int kHalves = 128 / BLOCK_N;
+      const int ch = et % BLOCK_N, half = et / BLOCK_N;
+      const int r0 = half * (kTileM / kHalves), r1 = r0 + kTileM / kHalves;
+      const float mu = p.fuse_mean[c_out0 + ch], rs = p.fuse_rstd[c_out0 + ch];
+      float sdz = 0.f, sdzx = 0.f;
+      for (int rr = r0; rr < r1; ++rr) {
+        const float g = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage + rr * S::kPitch + ch * 2));
+        const float xv = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage_x + rr * S::kPitch + ch * 2));
+        sdz += g;
+        sdzx += g * (xv - mu) * rs;
+      }
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.fuse_sums + c_out0 + ch),
+                (unsigned long long)__double2ll_rn((double)sdz * kGradSumScale));
+      atomicAdd(reinterpret_cast<unsigned long long*>(p.fuse_sums + p.out_C + c_out0 + ch),
+                (unsigned long long)__double2ll_rn((double)sdzx * kGradSumScale));
     }
   }
 
@@ -705,6 +778,29 @@ DPS_API int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int 
   if (rc) { delete pl; return rc; }
   pl->grid = dim3(nsplit, ny, 1);
   *out_plan = pl;
+  return 0;
+}
+
+// Fuse the following BatchNorm's backward reduction into a dgrad plan (see ConvParams::fuse_*).  sums: [2*C] int64,
+// zero on entry, fixed point x 2^40.  y / x: forward output and input of that BN, same shape as the plan's output.
+DPS_API int dps_conv_plan_fuse_bn_bwd(void* plan, const void* y, const void* x, const float* mean, const float* rstd,
+                                      long long* sums) {
+  ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
+  if (pl->kind != 1) DPS_FAIL(1, "fuse_bn_bwd: only dgrad plans");
+  pl->cp.fuse_y = reinterpret_cast<const __nv_bfloat16*>(y);
+  pl->cp.fuse_x = reinterpret_cast<const __nv_bfloat16*>(x);
+  pl->cp.fuse_mean = mean;
+  pl->cp.fuse_rstd = rstd;
+  pl->cp.fuse_sums = sums;
+  return 0;
+}
+
+// Stride-2 dgrad only: `addend` is [N][H/2][W/2][C] and is added to the output pixels of parity (0,0)
+// (the gradient coming back through a 1x1 stride-2 shortcut convolution).
+DPS_API int dps_conv_plan_addend_compact(void* plan, int on) {
+  ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
+  if (pl->kind != 1 || pl->cp.os != 2) DPS_FAIL(1, "addend_compact: only stride-2 dgrad plans");
+  pl->cp.addend_compact = on;
   return 0;
 }
 

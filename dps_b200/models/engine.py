@@ -31,6 +31,7 @@ def _decl() -> None:
     P, i32, i64, f32 = C.c_void_p, C.c_int, C.c_longlong, C.c_float
     L.declare("dps_bn_forward", i32, [P, P, P, P, P, P, P, P, P, P, P, i64, i32, i32, i32, f32, f32, P])
     L.declare("dps_bn_backward", i32, [P, P, P, P, P, P, P, P, P, P, P, i64, i32, i32, P])
+    L.declare("dps_bn_backward_apply", i32, [P, P, P, P, P, P, P, P, P, i64, i32, P])
     L.declare("dps_head_forward_backward", i32, [P] * 12 + [i32, i32, i32, i32, i32, P])
     L.declare("dps_stem_im2col", i32, [P, P, i32, i32, i32, P])
     _declared = True
@@ -121,6 +122,11 @@ class ResNetEngine:
         L.check(self.lib.dps_bn_backward(_p(dy), _p(y), _p(x), _p(bn.mean), _p(bn.rstd), _p(bn.gamma), _p(dz),
                                          _p(bn.bsums), _p(dx), _p(bn.dgamma), _p(bn.dbeta), bn.P, bn.C, int(relu),
                                          self._stream()), "bn_backward")
+
+    def _bn_bwd_apply(self, bn: _BN, dz, x, dx):
+        L.check(self.lib.dps_bn_backward_apply(_p(dz), _p(x), _p(bn.mean), _p(bn.rstd), _p(bn.gamma), _p(bn.bsums),
+                                               _p(dx), _p(bn.dgamma), _p(bn.dbeta), bn.P, bn.C, self._stream()),
+                "bn_backward_apply")
 
     # ------------------------------------------------------------------ graph construction
     def _conv_bn_unit(self, x, prefix_conv, prefix_bn, *, H, Cin, Cout, R, stride, relu, residual=None, stem=False):
@@ -220,47 +226,69 @@ class ResNetEngine:
         self.evalf.append(lambda: head(False))
 
         # ---------------- backward schedule ----------------
-        g_out = self.d_feat
-        for blk in reversed(blocks):
+        # Every dgrad epilogue also performs the backward *reduction* of the BatchNorm that consumes its output
+        # (masked gradient dz + per-channel sums), so most BNs only need the apply pass.  Stand-alone reductions
+        # remain for the last block's bn2 (fed by the head) and the three projection-shortcut BNs.
+        self.n_bn_full = self.n_bn_apply = 0
+
+        def bn_full(bn, dy, y, xx, dz, dx, relu):
+            self.bwd.append(lambda: self._bn_bwd(bn, dy, y, xx, dz, dx, relu))
+            self.n_bn_full += 1
+
+        def bn_apply(bn, dz, xx, dx):
+            self.bwd.append(lambda: self._bn_bwd_apply(bn, dz, xx, dx))
+            self.n_bn_apply += 1
+
+        def fuse(plan, unit):          # unit: the conv+BN unit whose BN consumes this dgrad's output
+            b = unit["bn"]
+            return plan.fuse_bn_bwd(unit["a"], unit["c"], b.mean, b.rstd, b.bsums)
+
+        g_out, g_out_fused = self.d_feat, False
+        for bi in range(len(blocks) - 1, -1, -1):
+            blk = blocks[bi]
             u1, u2, us = blk["u1"], blk["u2"], blk["us"]
             Cin, Cout, H, Ho, stride = blk["Cin"], blk["Cout"], blk["H"], blk["Ho"], blk["stride"]
+            prev_unit = blocks[bi - 1]["u2"] if bi > 0 else stem          # producer of this block's input
             g_c2 = self._bf(N, Ho, Ho, Cout)
             g_a1 = self._bf(N, Ho, Ho, Cout)
             g_c1 = self._bf(N, Ho, Ho, Cout)
             g_x = self._bf(N, H, H, Cin)
-            dz2 = g_out                                        # masked gradient written in place
-            self.bwd.append(lambda u2=u2, g_out=g_out, g_c2=g_c2:
-                            self._bn_bwd(u2["bn"], g_out, u2["a"], u2["c"], g_out, g_c2, True))
+            dz2 = g_out                                        # masked gradient lives in g_out
+            if g_out_fused:
+                bn_apply(u2["bn"], g_out, u2["c"], g_c2)
+            else:
+                bn_full(u2["bn"], g_out, u2["a"], u2["c"], g_out, g_c2, True)
             kw2 = dict(N=N, H=Ho, W=Ho, Cin=Cout, Cout=Cout, R=3, stride=1)
             p_w2 = ConvPlan.wgrad(u1["a"], g_c2, self._g(u2["wname"]), **kw2)
-            p_d2 = ConvPlan.dgrad(g_c2, self._w(u2["wname"]), g_a1, **kw2)
+            p_d2 = fuse(ConvPlan.dgrad(g_c2, self._w(u2["wname"]), g_a1, **kw2), u1)
             self.bwd += [p_w2.run, p_d2.run]
-            self.bwd.append(lambda u1=u1, g_a1=g_a1, g_c1=g_c1:
-                            self._bn_bwd(u1["bn"], g_a1, u1["a"], u1["c"], g_a1, g_c1, True))
+            bn_apply(u1["bn"], g_a1, u1["c"], g_c1)
             kw1 = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=3, stride=stride)
             p_w1 = ConvPlan.wgrad(blk["x"], g_c1, self._g(u1["wname"]), **kw1)
             self.bwd.append(p_w1.run)
             self._keep += [p_w2, p_d2, p_w1]
             if us is None:
-                p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=dz2, **kw1)
+                p_d1 = fuse(ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=dz2, **kw1), prev_unit)
                 self.bwd.append(p_d1.run)
                 self._keep.append(p_d1)
             else:
-                p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, **kw1)
+                # projection shortcut: its gradient is computed at half resolution first and added by the
+                # stride-2 dgrad of conv1 at the pixels of parity (0,0)
                 g_cs = self._bf(N, Ho, Ho, Cout)
+                g_s = self._bf(N, Ho, Ho, Cin)
+                bn_full(us["bn"], dz2, None, us["c"], None, g_cs, False)
                 kws = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=1, stride=stride)
                 p_ws = ConvPlan.wgrad(blk["x"], g_cs, self._g(us["wname"]), **kws)
-                p_ds = ConvPlan.dgrad(g_cs, self._w(us["wname"]), g_x, addend=g_x, **kws)
-                self.bwd.append(p_d1.run)
-                self.bwd.append(lambda us=us, dz2=dz2, g_cs=g_cs:
-                                self._bn_bwd(us["bn"], dz2, None, us["c"], None, g_cs, False))
-                self.bwd += [p_ws.run, p_ds.run]
-                self._keep += [p_d1, p_ws, p_ds]
-            g_out = g_x
+                p_ds = ConvPlan.dgrad(g_cs, self._w(us["wname"]), g_s, N=N, H=Ho, W=Ho, Cin=Cin, Cout=Cout, R=1,
+                                      stride=1)
+                p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=g_s, **kw1).addend_compact(True)
+                fuse(p_d1, prev_unit)
+                self.bwd += [p_ws.run, p_ds.run, p_d1.run]
+                self._keep += [p_ws, p_ds, p_d1]
+            g_out, g_out_fused = g_x, True
         # stem
         g_c0 = self._bf(N, S, S, STAGE_WIDTHS[0])
-        self.bwd.append(lambda stem=stem, g_out=g_out, g_c0=g_c0:
-                        self._bn_bwd(stem["bn"], g_out, stem["a"], stem["c"], g_out, g_c0, True))
+        bn_apply(stem["bn"], g_out, stem["c"], g_c0)
         p_w0 = ConvPlan.wgrad(self.col.view(N, S, S, 64), g_c0, self._g("conv1.weight"), N=N, H=S, W=S, Cin=64,
                               Cout=STAGE_WIDTHS[0], R=1, stride=1, valid_cols=STEM_PITCH, dw_pitch=STEM_PITCH)
         self.bwd.append(p_w0.run)
@@ -273,7 +301,7 @@ class ResNetEngine:
         n_conv = len(self.units)
         fwd = 1 + 1 + n_conv + n_bn + 2                      # memset, im2col, convs, bn, head(2)
         n_dgrad = n_conv - 1
-        bwd = 2 * n_bn + n_conv + n_dgrad
+        bwd = 2 * self.n_bn_full + self.n_bn_apply + n_conv + n_dgrad
         return fwd + bwd
 
     # ------------------------------------------------------------------ execution

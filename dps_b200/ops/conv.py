@@ -27,6 +27,8 @@ def _decl() -> None:
     L.declare("dps_wgrad_plan_create", i32, [P, P, P, i32, i32, i32, i32, i32, i32, i32, i32, i32, i32,
                                              C.POINTER(P)])
     L.declare("dps_conv_plan_run", i32, [P, P])
+    L.declare("dps_conv_plan_fuse_bn_bwd", i32, [P, P, P, P, P, P])
+    L.declare("dps_conv_plan_addend_compact", i32, [P, i32])
     L.declare("dps_conv_plan_destroy", i32, [P])
     L.declare("dps_conv_plan_info", i32, [P, C.POINTER(i32 * 3), C.POINTER(i32), C.POINTER(i32)])
     _declared = True
@@ -76,6 +78,17 @@ class ConvPlan:
         L.check(L.lib().dps_wgrad_plan_create(_ptr(x), _ptr(dy), _ptr(dw), N, H, W, Cin, Cout, R, stride, valid_cols,
                                               dw_pitch, nsplit, C.byref(h)), "wgrad_plan_create")
         return cls(h.value, cls.WGRAD, (x, dy, dw))
+
+    def fuse_bn_bwd(self, y, x, mean, rstd, sums) -> "ConvPlan":
+        """dgrad only: the epilogue also does the next BatchNorm's backward reduction (dz = dy*(y>0), sums)."""
+        L.check(L.lib().dps_conv_plan_fuse_bn_bwd(C.c_void_p(self.handle), _ptr(y), _ptr(x), _ptr(mean), _ptr(rstd),
+                                                  _ptr(sums)), "conv_plan_fuse_bn_bwd")
+        self._keep = self._keep + (y, x, mean, rstd, sums)
+        return self
+
+    def addend_compact(self, on: bool = True) -> "ConvPlan":
+        L.check(L.lib().dps_conv_plan_addend_compact(C.c_void_p(self.handle), int(on)), "conv_plan_addend_compact")
+        return self
 
     def run(self, stream=None) -> None:
         L.check(L.lib().dps_conv_plan_run(C.c_void_p(self.handle), C.c_void_p(L.stream_ptr(stream))), "conv_plan_run")

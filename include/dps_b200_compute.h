@@ -24,6 +24,11 @@ int dps_conv_plan_create(int kind, const void* x, const void* w, void* out, cons
 /* wgrad: dw[Cout][dw_pitch] fp32 += dY^T * im2col(x)   (atomic accumulation: the caller zeroes dw) */
 int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int N, int H, int W, int Cin, int Cout, int R,
                           int stride, int valid_cols, int dw_pitch, int nsplit, void** out_plan);
+/* dgrad plans only: also perform the next BatchNorm's backward reduction in the epilogue (writes dz = dy*(y>0),
+ * accumulates [2C] int64 sums x 2^40) / take the addend at half resolution for parity (0,0) (stride-2 only). */
+int dps_conv_plan_fuse_bn_bwd(void* plan, const void* y, const void* x, const float* mean, const float* rstd,
+                              long long* sums);
+int dps_conv_plan_addend_compact(void* plan, int on);
 int dps_conv_plan_run(void* plan, void* stream);
 int dps_conv_plan_destroy(void* plan);
 int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* smem_bytes);
@@ -35,10 +40,15 @@ int dps_bn_forward(const void* x, const long long* stats, const float* gamma, co
                    void* y, float* save_mean, float* save_rstd, float* running_mean, float* running_var,
                    long long* num_batches, long long P, int C, int relu, int training, float eps, float momentum,
                    void* stream);
-/* sums: [2C] fp64 scratch, zero on entry.  dz (masked gradient) may alias dy.  dgamma/dbeta are accumulated. */
+/* sums: [2C] int64 scratch (fixed point x 2^40), zero on entry.   dz (masked gradient) may alias dy.  dgamma/dbeta are accumulated. */
 int dps_bn_backward(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
-                    const float* gamma, void* dz, double* sums, void* dx, float* dgamma, float* dbeta, long long P,
+                    const float* gamma, void* dz, long long* sums, void* dx, float* dgamma, float* dbeta, long long P,
                     int C, int relu, void* stream);
+
+/* Apply pass only: dz and the [2C] int64 sums were already produced by a dgrad plan with dps_conv_plan_fuse_bn_bwd. */
+int dps_bn_backward_apply(const void* dz, const void* x, const float* mean, const float* rstd, const float* gamma,
+                          const long long* sums, void* dx, float* dgamma, float* dbeta, long long P, int C,
+                          void* stream);
 
 /* No counterpart in the reference.  dps_bn_backward for callers that cannot allocate the [2*C] scratch
  * (memory fully owned by a fixed-budget pool, loops that cannot take cudaMalloc's device-wide sync, hooks that

@@ -1,0 +1,40 @@
+"""W17: one config object; the reference's flag and env-var names still work (reference:
+src/parameter_server/server.py:405-433, src/workers/worker.py:455-482)."""
+import pytest
+
+from dps_b200 import config as CFG
+
+
+def test_server_cli_reference_flags_and_env(monkeypatch):
+    monkeypatch.setenv("SERVER_MODE", "async")
+    monkeypatch.setenv("TOTAL_WORKERS_EXPECTED", "8")
+    monkeypatch.setenv("SERVER_PORT", "9123")
+    cfg = CFG.parse_server_cli([])
+    assert (cfg.mode, cfg.workers, cfg.port, cfg.lr, cfg.staleness_bound) == ("async", 8, 9123, 0.1, 5)
+    cfg = CFG.parse_server_cli(["--mode", "sync", "--workers", "2", "--lr", "0.05", "--port", "8001",
+                                "--staleness-bound", "9"])
+    assert (cfg.mode, cfg.workers, cfg.port, cfg.lr) == ("sync", 2, 8001, 0.05)
+    assert cfg.staleness_bound == 9          # Q8: the reference parses this flag and then drops it
+
+
+def test_worker_cli_reference_flags_and_env(monkeypatch):
+    monkeypatch.setenv("PARAMETER_SERVER_ADDRESS", "ps.internal:8000")
+    cfg = CFG.parse_worker_cli([])
+    assert (cfg.server, cfg.worker_name, cfg.epochs, cfg.batch_size, cfg.sync_steps) == \
+        ("ps.internal:8000", "worker-node", 3, 128, 1)
+    cfg = CFG.parse_worker_cli(["--server", "h:1", "--worker-name", "w7", "--epochs", "1", "--batch-size", "64",
+                                "--lr", "0.2", "--sync-steps", "4", "--compat-pickle"])
+    assert (cfg.server, cfg.worker_name, cfg.epochs, cfg.batch_size, cfg.lr, cfg.sync_steps, cfg.compat_pickle) == \
+        ("h:1", "w7", 1, 64, 0.2, 4, True)
+
+
+@pytest.mark.parametrize("bad", [dict(workers=0), dict(workers=33), dict(mode="bsp"), dict(sync_steps=0),
+                                 dict(bn_buffer_policy="x"), dict(compress="int8")])
+def test_validation(bad):
+    with pytest.raises(ValueError):
+        CFG.Config(**bad).validate()
+
+
+def test_config_roundtrips_into_metrics():
+    d = CFG.Config(mode="async", workers=4).to_dict()
+    assert d["mode"] == "async" and d["workers"] == 4 and "staleness_bound" in d

@@ -120,3 +120,38 @@ def test_full_batch_layer1_shape():
     ref = F.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), padding=1).permute(0, 2, 3, 1)
     torch.cuda.synchronize()
     assert _relerr(out, ref) < 1.5e-2
+
+
+@pytest.mark.parametrize("shape", [(32, 64, 64, 3, 1), (16, 128, 128, 3, 1), (32, 64, 128, 3, 2), (8, 256, 512, 3, 2)],
+                         ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_dgrad_with_fused_bn_backward_reduction(shape):
+    """dgrad epilogue = dgrad (+addend) then the next BN's backward reduction: dz = dx*(y>0), sum(dz), sum(dz*xhat)."""
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    x, w, dy = _mk(*shape)
+    _, dx_ref, _ = _ref(x, w, dy, R, stride)
+    g = torch.Generator(device="cuda").manual_seed(7)
+    ybn = torch.randn(N, H, H, Cin, device="cuda", generator=g).to(torch.bfloat16)      # forward output of that BN
+    xbn = torch.randn(N, H, H, Cin, device="cuda", generator=g).to(torch.bfloat16)      # its input (conv output)
+    mean = torch.randn(Cin, device="cuda", generator=g) * 0.1
+    rstd = torch.rand(Cin, device="cuda", generator=g) + 0.5
+    sums = torch.zeros(2 * Cin, device="cuda", dtype=torch.int64)
+    dz = torch.empty(N, H, H, Cin, device="cuda", dtype=torch.bfloat16)
+    if stride == 2:      # shortcut gradient arrives at half resolution and lands on parity (0,0)
+        half = (torch.randn(N, H // 2, H // 2, Cin, device="cuda", generator=g) * 0.5).to(torch.bfloat16)
+        plan = ConvPlan.dgrad(dy, w, dz, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride, addend=half)
+        plan.addend_compact(True)
+        dx_ref = dx_ref.clone()
+        dx_ref[:, 0::2, 0::2] += half.float()
+    else:
+        plan = ConvPlan.dgrad(dy, w, dz, N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride)
+    plan.fuse_bn_bwd(ybn, xbn, mean, rstd, sums).run()
+    torch.cuda.synchronize()
+    want_dz = dx_ref * (ybn.float() > 0)
+    assert _relerr(dz, want_dz) < 2e-2
+    assert torch.equal(dz.float() == 0, (dz.float() == 0) | (ybn.float() <= 0))
+    dzf = dz.float().reshape(-1, Cin)
+    xhat = (xbn.float().reshape(-1, Cin) - mean) * rstd
+    got = sums.double() / 2 ** 40
+    assert torch.allclose(got[:Cin].float(), dzf.sum(0), rtol=2e-3, atol=5e-2)
+    assert torch.allclose(got[Cin:].float(), (dzf * xhat).sum(0), rtol=2e-3, atol=5e-2)

@@ -118,3 +118,24 @@ def test_training_reduces_loss_with_ps_on_one_gpu():
     sd = job.server.state_dict()
     assert len(sd) == 122 and float(sd["bn1.running_mean"].abs().sum()) > 0
     job.close()
+
+
+def test_launcher_one_gpu_end_to_end(tmp_path):
+    """W18: `python -m dps_b200.launch` trains, evaluates, checkpoints and aggregates metrics."""
+    import json
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    md, ck = tmp_path / "metrics", tmp_path / "ck.pt"
+    r = subprocess.run([sys.executable, "-m", "dps_b200.launch", "--gpus", "1", "--", "--mode", "sync", "--epochs", "2",
+                        "--batch-size", "32", "--train-samples", "256", "--test-samples", "64", "--lr", "0.05",
+                        "--metrics-dir", str(md), "--checkpoint", str(ck)], cwd=root, capture_output=True, text=True,
+                       timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    res = json.load(open(md / "sync_1workers.result.json"))
+    assert res["server_metrics"]["global_steps_completed"] == 16
+    agg = res["worker_metrics_aggregated"]
+    assert agg["num_workers"] == 1 and agg["total_local_steps"] == 16 and len(agg["accuracy_by_epoch"]) == 2
+    assert agg["images_per_second_sum"] > 0 and os.path.exists(ck)
+    assert r.stdout.count("METRICS_JSON:") == 2           # one worker record, one server record (Q11)

@@ -48,7 +48,7 @@ def _run(lib, L, noalloc, x, y, dy, mean, rstd, gamma, P, Cc):
         rc = lib.dps_bn_backward_noalloc(p(dy), p(y), p(x), p(mean), p(rstd), p(gamma), p(dz), p(dx), p(dgamma),
                                          p(dbeta), P, Cc, 1, st)
     else:
-        sums = torch.zeros(2 * Cc, device="cuda", dtype=torch.float64)
+        sums = torch.zeros(2 * Cc, device="cuda", dtype=torch.int64)
         rc = lib.dps_bn_backward(p(dy), p(y), p(x), p(mean), p(rstd), p(gamma), p(dz), p(sums), p(dx), p(dgamma),
                                  p(dbeta), P, Cc, 1, st)
     assert rc == 0, lib.dps_last_error()
