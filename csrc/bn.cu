@@ -43,6 +43,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
     float* __restrict__ running_var, long long* __restrict__ num_batches, long long P, int C, int relu,
     int training, float eps, float momentum) {
   __shared__ float s_scale[kMaxC], s_shift[kMaxC];
+  pdl_launch_dependents();
+  pdl_wait();
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var;
     if (training) {
@@ -114,6 +116,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
   // integer atomic per channel per CTA: integer adds are exact and order-independent, so the activation gradients
   // of a step are bit-reproducible run to run (bf16 re-rounding would otherwise amplify fp32 summation jitter).
   __shared__ float s_part[kBnThreads * 16];            // [row slot][2C] partials
+  pdl_launch_dependents();
+  pdl_wait();
   const int cg = C / 8;                               // channel groups; 256 % cg == 0
   const int my_cg = threadIdx.x % cg;
   const int rows_per_pass = blockDim.x / cg;
@@ -175,6 +179,8 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
     const float* __restrict__ rstd, const float* __restrict__ gamma, const long long* __restrict__ sums,
     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, long long P, int C) {
   __shared__ float s_a[kMaxC], s_b[kMaxC], s_c[kMaxC];   // dx = s_a*dz + s_b*x + s_c
+  pdl_launch_dependents();
+  pdl_wait();
   const float invP = 1.f / (float)P;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float sdz = (float)((double)sums[c] * (1.0 / kGradSumScale));
@@ -235,9 +241,9 @@ DPS_API int dps_bn_forward(const void* x, const long long* stats, const float* g
                            float* running_var, long long* num_batches, long long P, int C, int relu, int training,
                            float eps, float momentum, void* stream) {
   if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
-  bn_fwd_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+  DPS_CHECK(launch_pdl(bn_fwd_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)x, stats, gamma, beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, save_mean,
-      save_rstd, running_mean, running_var, num_batches, P, C, relu, training, eps, momentum);
+      save_rstd, running_mean, running_var, num_batches, P, C, relu, training, eps, momentum));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -251,13 +257,13 @@ DPS_API int dps_bn_backward(const void* dy, const void* y, const void* x, const 
   const int rows_per_pass = kBnThreads / (C / 8);
   long long want = (P + rows_per_pass - 1) / rows_per_pass;
   const int g1 = (int)(want < 148 * 4 ? (want < 1 ? 1 : want) : 148 * 4);
-  bn_bwd_reduce_kernel<<<g1, kBnThreads, 0, (cudaStream_t)stream>>>(
+  DPS_CHECK(launch_pdl(bn_bwd_reduce_kernel, dim3(g1), dim3(kBnThreads), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y, (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz,
-      sums, P, C, relu);
+      sums, P, C, relu));
   DPS_CHECK(cudaGetLastError());
-  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+  DPS_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)(relu ? dz : dy), (const __nv_bfloat16*)x, mean, rstd, gamma, sums, (__nv_bfloat16*)dx,
-      dgamma, dbeta, P, C);
+      dgamma, dbeta, P, C));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -266,9 +272,9 @@ DPS_API int dps_bn_backward_apply(const void* dz, const void* x, const float* me
                                   const float* gamma, const long long* sums, void* dx, float* dgamma, float* dbeta,
                                   long long P, int C, void* stream) {
   if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
-  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, (cudaStream_t)stream>>>(
+  DPS_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)dz, (const __nv_bfloat16*)x, mean, rstd, gamma, sums, (__nv_bfloat16*)dx, dgamma, dbeta,
-      P, C);
+      P, C));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -340,13 +346,13 @@ DPS_API int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x
   const int rows_per_pass = kBnThreads / (C / 8);
   long long want = (P + rows_per_pass - 1) / rows_per_pass;
   const int g1 = (int)(want < 148 * 4 ? (want < 1 ? 1 : want) : 148 * 4);
-  bn_bwd_reduce_kernel<<<g1, kBnThreads, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
+  DPS_CHECK(launch_pdl(bn_bwd_reduce_kernel, dim3(g1), dim3(kBnThreads), 0, st, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
                                                   (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz, sums, P, C,
-                                                  relu);
+                                                  relu));
   DPS_CHECK(cudaGetLastError());
-  bn_bwd_apply_kernel<<<bn_grid(P * (C / 8)), kBnThreads, 0, st>>>((const __nv_bfloat16*)(relu ? dz : dy),
+  DPS_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, st, (const __nv_bfloat16*)(relu ? dz : dy),
                                                                   (const __nv_bfloat16*)x, mean, rstd, gamma, sums,
-                                                                  (__nv_bfloat16*)dx, dgamma, dbeta, P, C);
+                                                                  (__nv_bfloat16*)dx, dgamma, dbeta, P, C));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

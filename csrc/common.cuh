@@ -30,7 +30,32 @@ extern thread_local char g_dps_err[512];
     return (code);                                           \
   } while (0)
 
+#include <cstdlib>
+#include <utility>
+
 namespace dps {
+
+// Host-side launch with the programmatic-stream-serialization attribute (DPS_PDL=0 turns it off).  Kernels
+// launched through this helper MUST call pdl_wait() before touching global memory written by their predecessor.
+inline bool pdl_enabled() {
+  static const bool on = [] { const char* e = getenv("DPS_PDL"); return !(e && e[0] == '0'); }();
+  return on;
+}
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kern)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  at[0].val.programmaticStreamSerializationAllowed = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = pdl_enabled() ? 1 : 0;
+  return cudaLaunchKernelEx(&cfg, kern, static_cast<KArgs>(std::forward<Args>(args))...);
+}
 
 // ------------------------------------------------------------------------------------------
 // misc
@@ -49,6 +74,12 @@ __device__ __forceinline__ bool elect_one() {
       : "=r"(pred));
   return pred != 0;
 }
+
+// Programmatic dependent launch: every compute kernel lets its successor start launching right away
+// (launch_dependents) and blocks before its first dependent global access until the predecessor grid has
+// completed and flushed (wait).  Hides launch latency and kernel prologues between the ~110 launches of a step.
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 
 __device__ __forceinline__ uint64_t globaltimer_ns() {
   uint64_t t;

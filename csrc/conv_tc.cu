@@ -103,6 +103,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   const int grp = blockIdx.z;
   const int ntaps = p.ntaps[grp];
@@ -133,6 +134,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();            // prologue above overlapped the previous kernel's tail; dependent data from here on
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -356,6 +358,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
   uint64_t* tmem_full = empty + kMaxStages;
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
 
+  pdl_launch_dependents();
   const int warp = threadIdx.x >> 5;
   // blockIdx.y enumerates (co_tile, ci_chunk, tap_group)
   int y = blockIdx.y;
@@ -389,6 +392,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();            // prologue above overlapped the previous kernel's tail; dependent data from here on
 
   if (warp == 0) {
     if (elect_one()) {
@@ -577,7 +581,7 @@ static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
                                    ConvSmem<BN_>::total(kMaxStages)));
     configured = true;
   }
-  kern<<<pl.grid, kThreads, ConvSmem<BN_>::total(pl.cp.nstages), st>>>(pl.tmA, pl.tmB, pl.cp);
+  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, pl.tmA, pl.tmB, pl.cp));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -591,7 +595,8 @@ static int launch_wgrad(const ConvPlan& pl, cudaStream_t st) {
                                    WgradSmem<NB_>::total(1, WgradSmem<NB_>::kBudget)));
     configured = true;
   }
-  kern<<<pl.grid, kThreads, WgradSmem<NB_>::total(pl.wp.nstages, pl.wp.stage_bytes), st>>>(pl.tmA, pl.tmB, pl.wp);
+  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kThreads), WgradSmem<NB_>::total(pl.wp.nstages, pl.wp.stage_bytes), st,
+                       pl.tmA, pl.tmB, pl.wp));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

@@ -34,6 +34,8 @@ __global__ void __launch_bounds__(kHeadThreads) head_sample_kernel(
     float* __restrict__ loss_n, int* __restrict__ correct_n, __nv_bfloat16* __restrict__ d_act, int N, int HW,
     int F, int K, int training) {
   __shared__ float s_pool[kMaxFeat];
+  pdl_launch_dependents();
+  pdl_wait();
   __shared__ float s_logit[kMaxClasses];
   __shared__ float s_red[2];
   const int n = blockIdx.x;
@@ -110,6 +112,8 @@ __global__ void __launch_bounds__(128) head_param_kernel(
     const int* __restrict__ correct_n, float* __restrict__ dw, float* __restrict__ db, float* __restrict__ out,
     int N, int F, int K, int training) {
   __shared__ float s_dl[1024];
+  pdl_launch_dependents();
+  pdl_wait();
   const int j = blockIdx.x;
   const int tid = threadIdx.x;
   if (training && j < K) {
@@ -157,6 +161,8 @@ __global__ void __launch_bounds__(128) head_param_kernel(
 // the same tcgen05 kernel as every other conv (reference stem: server.py:48).
 __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restrict__ img, __nv_bfloat16* __restrict__ col,
                                                           int N, int H, int W) {
+  pdl_launch_dependents();
+  pdl_wait();
   const long long total = (long long)N * H * W * 8;        // 8 vectors of 8 columns per pixel
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
@@ -192,12 +198,12 @@ DPS_API int dps_head_forward_backward(const void* act, const void* w, const floa
                                       void* stream) {
   if (F > kMaxFeat || F % 64 || K > kMaxClasses) DPS_FAIL(1, "head: unsupported F=%d K=%d", F, K);
   cudaStream_t st = (cudaStream_t)stream;
-  head_sample_kernel<<<N, kHeadThreads, 0, st>>>((const __nv_bfloat16*)act, (const __nv_bfloat16*)w, bias, labels,
+  DPS_CHECK(launch_pdl(head_sample_kernel, dim3(N), dim3(kHeadThreads), 0, st, (const __nv_bfloat16*)act, (const __nv_bfloat16*)w, bias, labels,
                                                  pooled, dlogits, loss_n, correct_n, (__nv_bfloat16*)d_act, N, HW, F,
-                                                 K, training);
+                                                 K, training));
   DPS_CHECK(cudaGetLastError());
-  head_param_kernel<<<dim3(training ? K : 1, training ? (F + 127) / 128 : 1), 128, 0, st>>>(
-      pooled, dlogits, loss_n, correct_n, dw, db, out, N, F, K, training);
+  DPS_CHECK(launch_pdl(head_param_kernel, dim3(training ? K : 1, training ? (F + 127) / 128 : 1), dim3(128), 0, st,
+      pooled, dlogits, loss_n, correct_n, dw, db, out, N, F, K, training));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -205,6 +211,8 @@ DPS_API int dps_head_forward_backward(const void* act, const void* w, const floa
 DPS_API int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* stream) {
   const long long total = (long long)N * H * W * 8;
   const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
+  // first kernel of a step: its predecessor is a memset / H2D copy node, so it is launched without the
+  // programmatic-dependency attribute (griddepcontrol.wait in the kernel is then a no-op)
   stem_im2col_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(img, (__nv_bfloat16*)col, N, H, W);
   DPS_CHECK(cudaGetLastError());
   return 0;
