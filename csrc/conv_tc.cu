@@ -54,11 +54,13 @@ struct Tap {
 };
 
 struct ConvParams {
-  int BW, BH, BN;                 // pixel box of a tile (BW*BH*BN == 128)
+  int BW, BH, BN;                 // pixel box of a tile (BW*BH*BN == 128), all powers of two
+  int bw_sh, bhw_sh;              // log2(BW), log2(BW*BH)
   int tiles_w, tiles_h;           // tiles along w and h (tiles along n = gridDim.x / (tiles_w*tiles_h))
   int red_blocks;                 // 64-wide reduction blocks per tap
   int ngroups;                    // parity groups (gridDim.z)
   int nstages;                    // pipeline depth (kMinStages or kMaxStages)
+  int tiles_total;                // halo kernel: number of 16x8-pixel tiles (persistent loop)
   int ntaps[4];
   Tap taps[4][9];
   int oph[4], opw[4];             // output parity offsets per group
@@ -86,8 +88,199 @@ struct ConvSmem {
   static constexpr int kStageBytes = kABytes + kBBytes;
   static constexpr int kPitch = BLOCK_N * 2 + 16;                 // staging row pitch (bank-conflict free)
   static constexpr int total(int nst) { return 1024 + nst * kStageBytes + kCtrlBytes; }   // 1024 = alignment slack
-  static_assert(2 * kTileM * kPitch <= kMinStages * kStageBytes, "two staging tiles must fit in the pipeline buffers");
+  static_assert(2 * kTileM * kPitch + 4096 <= kMinStages * kStageBytes, "staging must fit in the pipeline buffers");
 };
+
+// ---- explicit shared-space accessors (the staging tile is addressed with 32-bit shared addresses so the
+// compiler emits LDS/STS instead of generic loads) ----
+__device__ __forceinline__ uint4 lds_v4(uint32_t a) {
+  uint4 v;
+  asm volatile("ld.shared.v4.u32 {%0,%1,%2,%3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ uint32_t lds_u32(uint32_t a) {
+  uint32_t v;
+  asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ float lds_f32(uint32_t a) {
+  float v;
+  asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+  return v;
+}
+__device__ __forceinline__ void sts_v4(uint32_t a, uint4 v) {
+  asm volatile("st.shared.v4.u32 [%0], {%1,%2,%3,%4};" ::"r"(a), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ void sts_f32(uint32_t a, float v) {
+  asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+}
+__device__ __forceinline__ void red_fixed(long long* dst, float v, float scale) {
+  // exact: power-of-two scaling in fp32, then float -> int64 (no FP64 pipe involved)
+  atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)__float2ll_rn(v * scale));
+}
+
+// Epilogue shared by the conv kernels, executed by EPI_WARPS warps (threads 64 .. 64+32*EPI_WARPS):
+// TMEM accumulator -> bf16 staging tile -> (BN statistics | addend + fused BN-backward reduction) -> coalesced stores.
+// Warp w may only read TMEM lanes of quadrant (w & 3); with 8 warps each quadrant is split in two column halves.
+template <int BLOCK_N, int EPI_WARPS>
+__device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int n0, int h0, int w0, int c_out0,
+                                              uint32_t stage, uint32_t tmem_acc, uint64_t* tmem_full,
+                                              uint32_t full_parity, uint64_t* tmem_empty) {
+  constexpr int T = EPI_WARPS * 32;
+  constexpr int kPitch = ConvSmem<BLOCK_N>::kPitch;
+  constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
+  constexpr int kRowsPerPass = T / kChunks;
+  constexpr int kPasses = kTileM / kRowsPerPass;
+  constexpr int kGroup = kPasses < 4 ? kPasses : 4;
+  constexpr int kColsPerWarp = BLOCK_N / (EPI_WARPS / 4);
+  constexpr int kPairs = BLOCK_N / 2;                   // reductions work on bf16 pairs
+  constexpr int kParts = T / kPairs;                    // row partitions of the column reductions
+  constexpr int kRowsPerPart = kTileM / kParts;
+  const int et = threadIdx.x - 64;
+  const int ew = et >> 5, lane = et & 31;
+  const int q = (threadIdx.x >> 5) & 3;                 // TMEM lane quadrant of this warp
+  const int row = q * 32 + lane;                        // tile row == pixel index in the box
+  const int col0 = (ew >> 2) * kColsPerWarp;
+  const uint32_t stage_x = stage + kTileM * kPitch;     // second staging tile (x of the fused BN)
+  const uint32_t part_s = stage + 2 * kTileM * kPitch;  // [kParts][4][kPairs] fp32 partials
+  const int chunk = et % kChunks, row0 = et / kChunks;
+  const bool fuse = p.fuse_y != nullptr;
+  const bool use_addend = p.addend != nullptr && (!p.addend_compact || (p.oph[grp] == 0 && p.opw[grp] == 0));
+  // box dims are powers of two: shifts instead of divisions
+  const int bw_sh = p.bw_sh, bhw_sh = p.bhw_sh, bw_m = (1 << bw_sh) - 1, bhw_m = (1 << bhw_sh) - 1;
+  auto out_off = [&](int rr) -> size_t {
+    const int n = n0 + (rr >> bhw_sh), rem = rr & bhw_m;
+    const int oh = (h0 + (rem >> bw_sh)) * p.os + p.oph[grp], ow = (w0 + (rem & bw_m)) * p.os + p.opw[grp];
+    return (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
+  };
+  auto addend_off = [&](int rr) -> size_t {
+    if (!p.addend_compact) return out_off(rr);
+    const int n = n0 + (rr >> bhw_sh), rem = rr & bhw_m;
+    return (((size_t)n * (p.out_H / p.os) + h0 + (rem >> bw_sh)) * (p.out_W / p.os) + w0 + (rem & bw_m)) * p.out_C +
+           c_out0 + chunk * 8;
+  };
+  // Operands that do not depend on the accumulator (residual-gradient addend, y / x of the fused BN) are fetched
+  // in groups of kGroup rows, all loads of a group in flight at once; the first group is issued BEFORE waiting
+  // for the MMAs so its latency hides under the mainloop.
+  uint4 aa[kGroup], ya[kGroup], xa[kGroup];
+  auto issue = [&](int g) {
+#pragma unroll
+    for (int j = 0; j < kGroup; ++j) {
+      const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+      if (use_addend) aa[j] = ld_nc_v4(p.addend + addend_off(rr));
+      if (fuse) {
+        const size_t off = out_off(rr);
+        ya[j] = ld_nc_v4(p.fuse_y + off);
+        xa[j] = ld_nc_v4(p.fuse_x + off);
+      }
+    }
+  };
+  if (use_addend || fuse) issue(0);
+  mbar_wait(tmem_full, full_parity);
+  tc_fence_after();
+#pragma unroll
+  for (int c = 0; c < kColsPerWarp / 32; ++c) {
+    uint32_t r[32];
+    tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + col0 + c * 32, r);
+    tmem_ld_wait();
+    const uint32_t dst = stage + row * kPitch + (col0 + c * 32) * 2;
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      sts_v4(dst + j * 16,
+             make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]))));
+    }
+  }
+  tc_fence_before();
+  if (tmem_empty != nullptr) {             // persistent kernels: the accumulator may be overwritten from here on
+    __syncwarp();
+    if (lane == 0) mbar_arrive(tmem_empty);
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");      // epilogue warps only
+
+  const int pair = et % kPairs, part = et / kPairs;
+  // deterministic two-level column reduction: per-thread partial over its rows -> shared -> fixed-order sum ->
+  // ONE 64-bit fixed-point atomic per channel and tile
+  auto reduce_store = [&](float a0, float a1, float b0, float b1, long long* dst, int cstride, float sc0, float sc1) {
+    sts_f32(part_s + ((part * 4 + 0) * kPairs + pair) * 4, a0);
+    sts_f32(part_s + ((part * 4 + 1) * kPairs + pair) * 4, a1);
+    sts_f32(part_s + ((part * 4 + 2) * kPairs + pair) * 4, b0);
+    sts_f32(part_s + ((part * 4 + 3) * kPairs + pair) * 4, b1);
+    asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");
+    for (int idx = et; idx < 2 * BLOCK_N; idx += T) {
+      const int which = idx / BLOCK_N, ch = idx % BLOCK_N;
+      const int k = which * 2 + (ch & 1), pr = ch >> 1;
+      float acc = 0.f;
+#pragma unroll
+      for (int pp = 0; pp < kParts; ++pp) acc += lds_f32(part_s + ((pp * 4 + k) * kPairs + pr) * 4);
+      red_fixed(dst + which * cstride + c_out0 + ch, acc, which ? sc1 : sc0);
+    }
+  };
+
+  if (p.stats != nullptr) {
+    // fused BatchNorm statistics over the bf16 values that are actually stored
+    float s0 = 0.f, s1 = 0.f, q0 = 0.f, q1 = 0.f;
+    const uint32_t base = stage + (part * kRowsPerPart) * kPitch + pair * 4;
+#pragma unroll 8
+    for (int rr = 0; rr < kRowsPerPart; ++rr) {
+      const float2 v = unpack_bf16x2(lds_u32(base + rr * kPitch));
+      s0 += v.x; s1 += v.y;
+      q0 += v.x * v.x; q1 += v.y * v.y;
+    }
+    reduce_store(s0, s1, q0, q1, p.stats, p.out_C, (float)kStatSumScale, (float)kStatSqScale);
+  }
+
+#pragma unroll 1
+  for (int g = 0; g < kPasses / kGroup; ++g) {
+    if (g > 0) issue(g);
+#pragma unroll
+    for (int j = 0; j < kGroup; ++j) {
+      const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+      const size_t off = out_off(rr);
+      uint4 v = lds_v4(stage + rr * kPitch + chunk * 16);
+      if (use_addend) {
+        const uint4 a = aa[j];
+        float2 x, y;
+        x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
+      }
+      if (fuse) {
+        const uint4 yv = ya[j];
+        // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
+        auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
+          const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
+          const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
+          return gg & (lo | hi);
+        };
+        v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
+        sts_v4(stage + rr * kPitch + chunk * 16, v);       // dz, for the reduction below
+        sts_v4(stage_x + rr * kPitch + chunk * 16, xa[j]);
+      }
+      st_v4(p.out + off, v);
+    }
+  }
+  if (fuse) {
+    asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");
+    const float mu0 = p.fuse_mean[c_out0 + 2 * pair], mu1 = p.fuse_mean[c_out0 + 2 * pair + 1];
+    const float rs0 = p.fuse_rstd[c_out0 + 2 * pair], rs1 = p.fuse_rstd[c_out0 + 2 * pair + 1];
+    float d0 = 0.f, d1 = 0.f, x0 = 0.f, x1 = 0.f;
+    const uint32_t off = (part * kRowsPerPart) * kPitch + pair * 4;
+#pragma unroll 8
+    for (int rr = 0; rr < kRowsPerPart; ++rr) {
+      const float2 g = unpack_bf16x2(lds_u32(stage + off + rr * kPitch));
+      const float2 xv = unpack_bf16x2(lds_u32(stage_x + off + rr * kPitch));
+      d0 += g.x; d1 += g.y;
+      x0 += g.x * (xv.x - mu0) * rs0;
+      x1 += g.y * (xv.y - mu1) * rs1;
+    }
+    reduce_store(d0, d1, x0, x1, p.fuse_sums, p.out_C, (float)kGradSumScale, (float)kGradSumScale);
+  }
+  if (tmem_empty != nullptr) asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");   // staging is reused by the next tile
+}
 
 template <int BLOCK_N, bool B_MN>
 __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -182,130 +375,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     }
   } else {
     // ===================== epilogue (4 warps) =====================
-    const int q = warp & 3;                // TMEM lane quadrant this warp may access
-    const int row = q * 32 + lane_id();    // tile row == pixel index in the box
-    // Epilogue-side operands that do not depend on the accumulator (residual-gradient addend, and y / x of the BN
-    // whose backward reduction is fused here) are fetched in groups of kGroup rows with all loads of a group in
-    // flight at once; the first group is issued BEFORE waiting for the MMAs, so its latency hides under the mainloop.
-    constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
-    constexpr int kRowsPerPass = 128 / kChunks;
-    constexpr int kPasses = kTileM / kRowsPerPass;        // 8 (N=64) or 16 (N=128)
-    constexpr int kGroup = 4;
-    const int et = threadIdx.x - 64;                      // 0..127
-    const int chunk = et % kChunks, row0 = et / kChunks;
-    const int boxhw = p.BW * p.BH;
-    const bool fuse = p.fuse_y != nullptr;
-    const bool use_addend = p.addend != nullptr && (!p.addend_compact || (p.oph[grp] == 0 && p.opw[grp] == 0));
-    auto out_off = [&](int rr) -> size_t {
-      const int n = n0 + rr / boxhw, rem = rr % boxhw;
-      const int oh = (h0 + rem / p.BW) * p.os + p.oph[grp], ow = (w0 + rem % p.BW) * p.os + p.opw[grp];
-      return (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
-    };
-    auto addend_off = [&](int rr) -> size_t {
-      if (!p.addend_compact) return out_off(rr);
-      const int n = n0 + rr / boxhw, rem = rr % boxhw;
-      return (((size_t)n * (p.out_H / p.os) + h0 + rem / p.BW) * (p.out_W / p.os) + w0 + rem % p.BW) * p.out_C +
-             c_out0 + chunk * 8;
-    };
-    uint4 aa[kGroup], ya[kGroup], xa[kGroup];
-    auto issue = [&](int g) {
-#pragma unroll
-      for (int j = 0; j < kGroup; ++j) {
-        const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
-        if (use_addend) aa[j] = ld_nc_v4(p.addend + addend_off(rr));
-        if (fuse) {
-          const size_t off = out_off(rr);
-          ya[j] = ld_nc_v4(p.fuse_y + off);
-          xa[j] = ld_nc_v4(p.fuse_x + off);
-        }
-      }
-    };
-    if (use_addend || fuse) issue(0);
-    mbar_wait(tmem_full, 0);
-    tc_fence_after();
-    uint8_t* stage = stages;               // pipeline buffers are idle now: reuse as staging
-    uint8_t* stage_x = stage + kTileM * S::kPitch;        // second staging tile (x of the fused BN)
-#pragma unroll
-    for (int c = 0; c < BLOCK_N / 32; ++c) {
-      uint32_t r[32];
-      tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + c * 32, r);
-      tmem_ld_wait();
-      uint4* dst = reinterpret_cast<uint4*>(stage + row * S::kPitch + c * 64);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        dst[j] = make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
-                            pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
-                            pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
-                            pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7])));
-      }
-    }
-    tc_fence_before();
-    asm volatile("bar.sync 1, 128;" ::: "memory");      // epilogue warps only
-    if (p.stats != nullptr) {
-      // fused BatchNorm statistics over the bf16 values that are actually stored
-      constexpr int kHalves = 128 / BLOCK_N;              // 2 for N=64, 1 for N=128
-      const int ch = et % BLOCK_N, half = et / BLOCK_N;
-      const int r0 = half * (kTileM / kHalves), r1 = r0 + kTileM / kHalves;
-      float s = 0.f, ss = 0.f;
-      for (int rr = r0; rr < r1; ++rr) {
-        const float v = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage + rr * S::kPitch + ch * 2));
-        s += v;
-        ss += v * v;
-      }
-      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + c_out0 + ch),
-                (unsigned long long)__double2ll_rn((double)s * kStatSumScale));
-      atomicAdd(reinterpret_cast<unsigned long long*>(p.stats + p.out_C + c_out0 + ch),
-                (unsigned long long)__double2ll_rn((double)ss * kStatSqScale));
-    }
-
-    for (int g = 0; g < kPasses / kGroup; ++g) {
-      if (g > 0) issue(g);
-#pragma unroll
-      for (int j = 0; j < kGroup; ++j) {
-        const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
-        const size_t off = out_off(rr);
-        uint4 v = *reinterpret_cast<const uint4*>(stage + rr * S::kPitch + chunk * 16);
-        if (use_addend) {
-          const uint4 a = aa[j];
-          float2 x, y;
-          x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
-          x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
-          x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
-          x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
-        }
-        if (fuse) {
-          const uint4 yv = ya[j];
-          // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
-          auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
-            const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
-            const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
-            return gg & (lo | hi);
-          };
-          v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
-          *reinterpret_cast<uint4*>(stage + rr * S::kPitch + chunk * 16) = v;       // dz, for the reduction below
-          *reinterpret_cast<uint4*>(stage_x + rr * S::kPitch + chunk * 16) = xa[j];
-        }
-        st_v4(p.out + off, v);
-      }
-    }
-    if (fuse) {
-      asm volatile("bar.sync 1, 128;" ::: "memory");
-      constexpr int kHalves = 128 / BLOCK_N;
-      const int ch = et % BLOCK_N, half = et / BLOCK_N;
-      const int r0 = half * (kTileM / kHalves), r1 = r0 + kTileM / kHalves;
-      const float mu = p.fuse_mean[c_out0 + ch], rs = p.fuse_rstd[c_out0 + ch];
-      float sdz = 0.f, sdzx = 0.f;
-      for (int rr = r0; rr < r1; ++rr) {
-        const float g = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage + rr * S::kPitch + ch * 2));
-        const float xv = __bfloat162float(*reinterpret_cast<const __nv_bfloat16*>(stage_x + rr * S::kPitch + ch * 2));
-        sdz += g;
-        sdzx += g * (xv - mu) * rs;
-      }
-      atomicAdd(reinterpret_cast<unsigned long long*>(p.fuse_sums + c_out0 + ch),
-                (unsigned long long)__double2ll_rn((double)sdz * kGradSumScale));
-      atomicAdd(reinterpret_cast<unsigned long long*>(p.fuse_sums + p.out_C + c_out0 + ch),
-                (unsigned long long)__double2ll_rn((double)sdzx * kGradSumScale));
-    }
+    conv_epilogue<BLOCK_N, 4>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
   }
 
   tc_fence_before();
@@ -313,6 +383,135 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BLOCK_N);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// haloconv_kernel: 3x3 stride-1 convolutions with 64 reduction channels and 64 output channels (layer1 fprop
+// and dgrad), persistent, weights resident.
+//
+// tapconv re-reads the activation box once per filter tap and the whole weight matrix once per pixel tile: for
+// layer1 that is 216 KB of L2->SM traffic per 128x64 output tile, which bounds the kernel (profiles/
+// ncu_tapconv_layer1_fprop.md).  Here each CTA keeps the 9 x 64 x 64 weights (72 KB) in shared memory for its whole
+// life and loads ONE halo tile of (16+2) x (8+2) pixels x 64 channels per output tile (23 KB, TMA zero-fills the
+// padding).  Each filter tap is then just a *shifted window* of that halo tile: the UMMA A descriptor starts at
+// ((1+dh)*10 + (1+dw)) * 128 B with a stride-byte-offset of 10 * 128 B between 8-row groups -- one image row of the
+// 16x8 tile is one 8-row group.  (The 128-byte swizzle is a function of absolute shared-memory address bits, so
+// windows that are not 1024-byte aligned read correctly with base_offset = 0; probed in csrc/exp_halo.cu.)
+// Two 64-column TMEM accumulators let the epilogue of tile i overlap the MMAs of tile i+1.
+// ------------------------------------------------------------------------------------------
+constexpr int kHaloW = 8, kHaloH = 16;
+constexpr int kHaloRowsW = kHaloW + 2;
+constexpr int kHaloBytes = (kHaloH + 2) * kHaloRowsW * 128;      // 23040
+constexpr int kHaloSlot = 23552;                                  // rounded up to 1024
+constexpr int kHaloSlots = 4;
+constexpr int kHaloWBytes = 9 * 8192;
+constexpr int kHaloEpiWarps = 8;
+constexpr int kHaloThreads = 64 + 32 * kHaloEpiWarps;
+constexpr int kHaloStaging = 2 * kTileM * ConvSmem<64>::kPitch + 4096;   // dz + x tiles + reduction partials
+constexpr int kHaloSmem = 1024 + kHaloWBytes + kHaloSlots * kHaloSlot + kHaloStaging + 256;
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                               const __grid_constant__ CUtensorMap tmB,
+                                                               const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;
+  uint8_t* sA = sW + kHaloWBytes;
+  uint8_t* staging = sA + kHaloSlots * kHaloSlot;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(staging + kHaloStaging);
+  uint64_t* fullA = wfull + 1;
+  uint64_t* emptyA = fullA + kHaloSlots;
+  uint64_t* tfull = emptyA + kHaloSlots;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      mbar_init(wfull, 1);
+      for (int s = 0; s < kHaloSlots; ++s) { mbar_init(&fullA[s], 1); mbar_init(&emptyA[s], 1); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], kHaloEpiWarps); }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 128);            // two 64-column accumulators
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+  if (warp == 0) {
+    if (elect_one()) {
+      mbar_expect_tx(wfull, kHaloWBytes);
+      for (int t = 0; t < 9; ++t) {
+        if (!B_MN) tma_load_2d(sW + t * 8192, &tmB, wfull, p.taps[0][t].k_off, 0);     // [64 co rows][64 k]
+        else       tma_load_2d(sW + t * 8192, &tmB, wfull, p.taps[0][t].k_off, 0);     // [64 co(k) rows][64 ci]
+      }
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+        const int s = i % kHaloSlots, ph = (i / kHaloSlots) & 1;
+        const int n = t / tiles_per_img, r = t % tiles_per_img;
+        const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
+        mbar_wait(&emptyA[s], ph ^ 1);
+        mbar_expect_tx(&fullA[s], kHaloBytes);
+        tma_load_5d(sA + s * kHaloSlot, &tmA, &fullA[s], 0, w0 - 1, 0, h0 - 1, n);
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(kTileM, 64, 0, B_MN ? 1 : 0);
+      mbar_wait(wfull, 0);
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+        const int s = i % kHaloSlots, ph = (i / kHaloSlots) & 1;
+        const int acc = i & 1;
+        mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);          // epilogue has drained this accumulator
+        mbar_wait(&fullA[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(sA + s * kHaloSlot);
+#pragma unroll
+        for (int tp = 0; tp < 9; ++tp) {
+          const Tap tap = p.taps[0][tp];
+          const uint32_t a_addr = a_base + ((1 + tap.da) * kHaloRowsW + (1 + tap.db)) * 128;
+          const uint64_t adesc = make_smem_desc(a_addr, 16, kHaloRowsW * 128);
+          const uint32_t b_addr = smem_u32(sW + tp * 8192);
+          const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+          for (int k = 0; k < 4; ++k)
+            umma_bf16(tmem_base + acc * 64, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(B_MN ? k * 128 : k * 2), idesc,
+                      (tp | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&emptyA[s]);
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else {
+    int i = 0;
+    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+      const int n = t / tiles_per_img, r = t % tiles_per_img;
+      const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
+      const int acc = i & 1;
+      conv_epilogue<64, kHaloEpiWarps>(p, 0, n, h0, w0, 0, smem_u32(staging), tmem_base + acc * 64, &tfull[acc],
+                                       (i >> 1) & 1, &tempty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
   }
 }
 
@@ -565,6 +764,7 @@ struct ConvPlan {
   int kind;                       // 0 fprop, 1 dgrad, 2 wgrad
   int block_n;
   bool b_mn;
+  bool halo;                      // persistent halo kernel (layer1-type convs)
   CUtensorMap tmA, tmB;
   ConvParams cp;
   WgradParams wp;
@@ -583,6 +783,18 @@ static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
   }
   DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, pl.tmA, pl.tmB, pl.cp));
   DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+template <bool MN_>
+static int launch_halo(const ConvPlan& pl, cudaStream_t st) {
+  auto kern = haloconv_kernel<MN_>;
+  static bool configured = false;
+  if (!configured) {
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kHaloSmem));
+    configured = true;
+  }
+  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kHaloThreads), kHaloSmem, st, pl.tmA, pl.tmB, pl.cp));
   return 0;
 }
 
@@ -639,10 +851,19 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   // pixel tiles run over the conv OUTPUT grid for fprop, and over the dY-resolution grid for dgrad
   // (stride 1: same as dX; stride 2: one tile of (a, b) per output-parity class)
   const int TH = Ho, TW = Wo;
-  if (!pick_box(kTileM, N, TH, TW, &cp.BW, &cp.BH, &cp.BN)) {
+  {
+    const char* e = getenv("DPS_HALO");
+    pl->halo = !(e && e[0] == '0') && R == 3 && stride == 1 && red == 64 && ngemm == 64 && H % kHaloH == 0 &&
+               W % kHaloW == 0;
+  }
+  if (pl->halo) {
+    cp.BW = kHaloW; cp.BH = kHaloH; cp.BN = 1;
+  } else if (!pick_box(kTileM, N, TH, TW, &cp.BW, &cp.BH, &cp.BN)) {
     delete pl;
     DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
   }
+  for (cp.bw_sh = 0; (1 << cp.bw_sh) < cp.BW; ++cp.bw_sh) {}
+  for (cp.bhw_sh = 0; (1 << cp.bhw_sh) < cp.BW * cp.BH; ++cp.bhw_sh) {}
   cp.tiles_w = TW / cp.BW;
   cp.tiles_h = TH / cp.BH;
   const int tiles_n = N / cp.BN;
@@ -670,7 +891,8 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         cp.taps[0][nt++] = t;
       }
     cp.ntaps[0] = nt;
-    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW, cp.BH, cp.BN);
+    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (pl->halo ? 2 : 0), cp.BH + (pl->halo ? 2 : 0),
+                      cp.BN);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->block_n);
   } else {
     cp.out_H = H; cp.out_W = W; cp.out_C = Cin; cp.os = stride;
@@ -707,12 +929,17 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         }
       cp.ngroups = g;
     }
-    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW, cp.BH, cp.BN);
+    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW + (pl->halo ? 2 : 0), cp.BH + (pl->halo ? 2 : 0),
+                      cp.BN);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, 64);
   }
   if (rc) { delete pl; return rc; }
   pl->grid = dim3(cp.tiles_w * cp.tiles_h * tiles_n, ngemm / pl->block_n, cp.ngroups);
   cp.nstages = ((long long)pl->grid.x * pl->grid.y * pl->grid.z <= 148) ? kMaxStages : kMinStages;
+  if (pl->halo) {
+    cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
+    pl->grid = dim3(cp.tiles_total < 148 ? cp.tiles_total : 148, 1, 1);      // persistent: one CTA per SM
+  }
   *out_plan = pl;
   return 0;
 }
@@ -813,6 +1040,7 @@ DPS_API int dps_conv_plan_run(void* plan, void* stream) {
   ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
   cudaStream_t st = (cudaStream_t)stream;
   if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
+  if (pl->halo) return pl->b_mn ? launch_halo<true>(*pl, st) : launch_halo<false>(*pl, st);
   if (pl->b_mn) return pl->block_n == 128 ? launch_tapconv<128, true>(*pl, st) : launch_tapconv<64, true>(*pl, st);
   return pl->block_n == 128 ? launch_tapconv<128, false>(*pl, st) : launch_tapconv<64, false>(*pl, st);
 }
@@ -827,6 +1055,7 @@ DPS_API int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* sme
   grid_xyz[0] = pl->grid.x; grid_xyz[1] = pl->grid.y; grid_xyz[2] = pl->grid.z;
   *block_n = pl->block_n;
   *smem_bytes = pl->kind == 2 ? WgradSmem<64>::total(pl->wp.nstages, pl->wp.stage_bytes)
+                : pl->halo   ? kHaloSmem
                               : (pl->block_n == 128 ? ConvSmem<128>::total(pl->cp.nstages)
                                                     : ConvSmem<64>::total(pl->cp.nstages));
   return 0;
