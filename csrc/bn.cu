@@ -232,7 +232,7 @@ using namespace dps;
 
 static int bn_grid(long long nvec) {
   long long want = (nvec + kBnThreads - 1) / kBnThreads;
-  long long cap = 148 * 8;
+  long long cap = 148 * 3;      // exactly one wave at 3 CTAs / SM (77-80 registers): no partial last wave
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 

@@ -178,14 +178,30 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
   if (use_addend || fuse) issue(0);
   mbar_wait(tmem_full, full_parity);
   tc_fence_after();
+  if constexpr (kColsPerWarp >= 32) {
 #pragma unroll
-  for (int c = 0; c < kColsPerWarp / 32; ++c) {
-    uint32_t r[32];
-    tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + col0 + c * 32, r);
+    for (int c = 0; c < kColsPerWarp / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + col0 + c * 32, r);
+      tmem_ld_wait();
+      const uint32_t dst = stage + row * kPitch + (col0 + c * 32) * 2;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sts_v4(dst + j * 16,
+               make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]))));
+      }
+    }
+  } else {
+    static_assert(kColsPerWarp == 16 || kColsPerWarp >= 32, "unsupported epilogue split");
+    uint32_t r[16];
+    tmem_ld_32x16(tmem_acc + ((uint32_t)(q * 32) << 16) + col0, r);
     tmem_ld_wait();
-    const uint32_t dst = stage + row * kPitch + (col0 + c * 32) * 2;
+    const uint32_t dst = stage + row * kPitch + col0 * 2;
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
+    for (int j = 0; j < 2; ++j) {
       sts_v4(dst + j * 16,
              make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
                         pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
@@ -406,9 +422,9 @@ constexpr int kHaloBytes = (kHaloH + 2) * kHaloRowsW * 128;      // 23040
 constexpr int kHaloSlot = 23552;                                  // rounded up to 1024
 constexpr int kHaloSlots = 4;
 constexpr int kHaloWBytes = 9 * 8192;
-constexpr int kHaloEpiWarps = 8;
+constexpr int kHaloEpiWarps = 16;
 constexpr int kHaloThreads = 64 + 32 * kHaloEpiWarps;
-constexpr int kHaloStaging = 2 * kTileM * ConvSmem<64>::kPitch + 4096;   // dz + x tiles + reduction partials
+constexpr int kHaloStaging = 2 * kTileM * ConvSmem<64>::kPitch + 8192;   // dz + x tiles + reduction partials
 constexpr int kHaloSmem = 1024 + kHaloWBytes + kHaloSlots * kHaloSlot + kHaloStaging + 256;
 
 template <bool B_MN>
