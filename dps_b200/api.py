@@ -241,7 +241,7 @@ class Worker:
         use_graph = self.cfg.use_cuda_graph and self.engine_kind == "native"
         if use_graph and self.graph is None:
             self._build_graph()
-        self.engine.load_batch(images, labels)
+        self._stage_batch(images, labels)
         fused_exchange = use_graph and self.cfg.sync_steps == 1
         if use_graph:
             self.graph.replay()
@@ -262,6 +262,33 @@ class Worker:
         self.local_step_counter += 1
         self.images_seen += int(labels.numel())
         return LossHandle(self._ring[slot], self._events[slot])
+
+    def _stage_batch(self, images: torch.Tensor, labels: torch.Tensor) -> None:
+        """H2D of the batch on a side stream into one of two staging buffers (overlaps the previous step's
+        kernels), then a device-to-device hand-over into the engine's static input on the compute stream."""
+        if not (images.is_pinned() and labels.is_pinned()) or not hasattr(self.engine, "images"):
+            self.engine.load_batch(images, labels)
+            return
+        if not hasattr(self, "_copy_stream"):
+            self._copy_stream = torch.cuda.Stream(device=self.job.device)
+            self._stage_x = [torch.empty_like(self.engine.images) for _ in range(2)]
+            self._stage_y = [torch.empty_like(self.engine.labels) for _ in range(2)]
+            self._h2d_done = [torch.cuda.Event() for _ in range(2)]
+            self._consumed = [torch.cuda.Event() for _ in range(2)]
+            self._stage_uses = 0
+        k = self._stage_uses % 2
+        main = torch.cuda.current_stream()
+        with torch.cuda.stream(self._copy_stream):
+            if self._stage_uses >= 2:
+                self._copy_stream.wait_event(self._consumed[k])     # staging slot k was handed over two steps ago
+            self._stage_x[k].copy_(images, non_blocking=True)
+            self._stage_y[k].copy_(labels, non_blocking=True)
+            self._h2d_done[k].record(self._copy_stream)
+        main.wait_event(self._h2d_done[k])
+        self.engine.images.copy_(self._stage_x[k], non_blocking=True)
+        self.engine.labels.copy_(self._stage_y[k], non_blocking=True)
+        self._consumed[k].record(main)
+        self._stage_uses += 1
 
     # ------------------------------------------------------------------ evaluation
     @torch.no_grad()
