@@ -235,34 +235,39 @@ __global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__
   const long long lo = (long long)b * per, hi = min(E, lo + per);
   uint32_t* lf = T.flags[r];                                  // my local flag block
   uint32_t* of = T.flags[o];                                  // owner's flag block (peer)
-  __shared__ uint32_t s_ticket;
+  __shared__ uint32_t s_ticket, s_drop;
   if (threadIdx.x == 0) {
-    uint32_t ticket;
+    uint32_t ticket = 0, drop = 0;
     if (b == 0) {
-      ticket = atom_add_acqrel_sys(of + DPS_F_RING_TAIL, 1u);
-      // back-pressure: slot (ticket % R) is free once the consumer's head has passed ticket - R
-      const uint64_t t0 = globaltimer_ns();
-      while ((int32_t)(ld_acquire_sys(of + DPS_F_RING_HEAD) + (uint32_t)R - ticket) <= 0) {
-        __nanosleep(128);
-        if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) {
-          atomicOr(lf + DPS_F_ERROR, DPS_ERR_RING_FULL);
-          break;
-        }
+      // WAIT-FREE admission: a push never blocks on another rank (a rank stuck in push could not serve its own
+      // ring, and two such ranks would wait on each other).  Take a ticket only if the ring certainly has room:
+      // at most W producers can pass this check concurrently, hence the margin of W slots.  Otherwise the push to
+      // this shard is skipped for this step; the gradient slice is NOT zeroed, so it rides along with the next one.
+      const uint32_t tail = ld_acquire_sys(of + DPS_F_RING_TAIL), head = ld_acquire_sys(of + DPS_F_RING_HEAD);
+      if ((int32_t)(tail - head) > R - W) {
+        drop = 1;
+        atomicAdd(lf + DPS_F_DROPPED, 1u);
+      } else {
+        ticket = atom_add_acqrel_sys(of + DPS_F_RING_TAIL, 1u);
+        uint32_t* hdr = of + DPS_F_SLOTS + (ticket % R) * 4;
+        hdr[1] = (uint32_t)r;
+        hdr[2] = lf[DPS_F_SEEN + o];                          // version of shard o this worker last pulled
       }
-      uint32_t* hdr = of + DPS_F_SLOTS + (ticket % R) * 4;
-      hdr[1] = (uint32_t)r;
-      hdr[2] = lf[DPS_F_SEEN + o];                            // version of shard o this worker last pulled
-      // publish the ticket to the other CTAs of this (rank, owner) pair
+      // publish the decision to the other CTAs of this (rank, owner) pair
       lf[DPS_F_TICKET + 2 * o + 1] = ticket;
+      lf[DPS_F_DROP + o] = drop;
       __threadfence();
       st_release_sys(lf + DPS_F_TICKET + 2 * o, step + 1);
     } else {
       while (ld_acquire_sys(lf + DPS_F_TICKET + 2 * o) != step + 1) __nanosleep(32);
       ticket = lf[DPS_F_TICKET + 2 * o + 1];
+      drop = lf[DPS_F_DROP + o];
     }
     s_ticket = ticket;
+    s_drop = drop;
   }
   __syncthreads();
+  if (s_drop) return;
   const uint32_t ticket = s_ticket;
   const uint32_t slot = ticket % (uint32_t)R;
   uint16_t* dst = T.ring[o] + (long long)slot * E;

@@ -155,7 +155,8 @@ class ParameterServer:
                           "max_staleness_observed": max(last) if last else 0,
                           "running_mean_staleness": round(st["running_mean_staleness"], 4),
                           "running_max_staleness": st["running_max_staleness"],
-                          "staleness_histogram": st["staleness_histogram"], "torn_pulls": st["torn_pulls"]})
+                          "staleness_histogram": st["staleness_histogram"], "torn_pulls": st["torn_pulls"],
+                          "dropped_pushes": st["dropped_pushes"]})
         return M.server_final_metrics(mode=self.cfg.mode, total_workers=self.job.world, total_time=total,
                                       global_step=steps, total_updates=steps,
                                       gradients_processed=steps * (self.job.world if self.cfg.mode == "sync" else 1),

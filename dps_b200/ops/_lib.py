@@ -21,7 +21,7 @@ HIST_BINS = 16
 FLAG_WORDS = 1024
 
 # flag-block word offsets (mirror include/dps_b200.h)
-F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS = 0, 32, 33, 34, 35
+F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS, F_DROPPED = 0, 32, 33, 34, 35, 36
 F_HEARTBEAT, F_RING_TAIL, F_RING_HEAD, F_VERSION, F_PUBSEQ, F_APPLY_DONE = 64, 96, 97, 98, 99, 100
 F_SLOTS = 128
 F_STAT_ACCEPTED, F_STAT_REJECTED, F_STAT_SUM, F_STAT_MAX, F_STAT_HIST, F_STAT_LAST = 512, 513, 514, 515, 520, 544

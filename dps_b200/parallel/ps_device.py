@@ -190,11 +190,12 @@ class DevicePS:
         """Owner role: drain the arrival ring (non-blocking) and apply in ticket order."""
         o = self.rank if owner is None else owner
         cfg = self.cfg
-        L.check(self.lib.dps_async_apply(self._tp, o, self.async_ctas, cfg.staleness_bound, cfg.staleness_alpha,
-                                         cfg.staleness_floor, max_batch, lr if lr is not None else cfg.lr,
-                                         cfg.momentum, cfg.weight_decay, self.ctas, L.stream_ptr(stream)),
-                "async_apply")
-        self.launches += 2
+        for _ in range(max(1, (self.world + L.MAX_PLAN - 1) // L.MAX_PLAN)):     # W arrivals per step, 16 per pass
+            L.check(self.lib.dps_async_apply(self._tp, o, self.async_ctas, cfg.staleness_bound, cfg.staleness_alpha,
+                                             cfg.staleness_floor, max_batch, lr if lr is not None else cfg.lr,
+                                             cfg.momentum, cfg.weight_decay, self.ctas, L.stream_ptr(stream)),
+                    "async_apply")
+            self.launches += 2
 
     # ------------------------------------------------------------------ introspection
     def flag_words(self, rank: Optional[int] = None) -> torch.Tensor:
@@ -215,7 +216,7 @@ class DevicePS:
             "running_mean_staleness": f[L.F_STAT_SUM] / n, "running_max_staleness": f[L.F_STAT_MAX],
             "staleness_histogram": {str(i): f[L.F_STAT_HIST + i] for i in range(L.HIST_BINS) if f[L.F_STAT_HIST + i]},
             "last_staleness_per_worker": f[L.F_STAT_LAST:L.F_STAT_LAST + self.world],
-            "version": f[L.F_VERSION], "torn_pulls": f[L.F_TORN_PULLS],
+            "version": f[L.F_VERSION], "torn_pulls": f[L.F_TORN_PULLS], "dropped_pushes": f[L.F_DROPPED],
             "heartbeat": f[L.F_HEARTBEAT:L.F_HEARTBEAT + self.world],
         }
 

@@ -27,6 +27,7 @@ extern "C" {
 #define DPS_F_ERROR 33          /* sticky error bits (DPS_ERR_*)                                 */
 #define DPS_F_MISSING 34        /* mask of ranks missing at the last timed-out barrier           */
 #define DPS_F_TORN_PULLS 35     /* async pulls that stayed inconsistent after retries            */
+#define DPS_F_DROPPED 36        /* async pushes skipped because the owner's ring had no room     */
 #define DPS_F_HEARTBEAT 64      /* [32] last step seen from each source rank                     */
 #define DPS_F_RING_TAIL 96      /* async ring: next ticket (peer atomics)                        */
 #define DPS_F_RING_HEAD 97      /* async ring: tickets consumed                                  */
@@ -43,6 +44,7 @@ extern "C" {
 #define DPS_F_PLAN 640          /* n, new_version, new_head, slots[16], weights[16]              */
 #define DPS_F_TICKET 704        /* [32][2] local {tag, ticket} per owner                         */
 #define DPS_F_SEEN 800          /* [32] version of each shard at this worker's last pull         */
+#define DPS_F_DROP 832          /* [32] local: this step's push to owner o was skipped            */
 #define DPS_FLAG_WORDS 1024
 
 #define DPS_ERR_BARRIER_TIMEOUT 1u

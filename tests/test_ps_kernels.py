@@ -229,3 +229,32 @@ def test_checkpoint_resume_through_job(tmp_path):
     l = job2.worker.train_step(x, y).item()
     assert l == l and job2.server.global_step == 4
     job2.close()
+
+
+def test_async_push_is_wait_free_when_the_ring_is_full():
+    """A push never blocks on another rank: with no room in the owner's ring it is skipped, counted, and the
+    gradient slice is kept (not zeroed) so it is sent with the next push."""
+    W = 2
+    model, layout, ps, flat0 = _setup(W, mode="async", lr=0.1, async_ring_slots=1)      # R = 2: room for W - ... 
+    g = torch.randn(layout.total, device="cuda") * 0.01
+    ps.grad[0].copy_(g)
+    ps.push_async(0)                        # admitted on both shards (rings empty)
+    torch.cuda.synchronize()
+    assert float(ps.grad[0].abs().max()) == 0.0
+    ps.grad[0].copy_(g)
+    ps.push_async(0)                        # nobody served: no room (margin of W slots) -> skipped, not blocked
+    torch.cuda.synchronize()
+    assert ps.async_stats(0)["dropped_pushes"] == W
+    assert torch.equal(ps.grad[0], g)       # kept for the next push
+    for o in range(W):
+        ps.serve_async(o)
+    ps.push_async(0)                        # room again
+    torch.cuda.synchronize()
+    assert float(ps.grad[0].abs().max()) == 0.0 and ps.error_bits(0) == 0
+    for o in range(W):
+        ps.serve_async(o)
+    torch.cuda.synchronize()
+    want = flat0 - 0.1 * g.half().float() - 0.1 * g.half().float()      # two accepted pushes, staleness 0 then 1->w
+    st = ps.async_stats(0)
+    assert st["async_updates"] == 2
+    ps.close()
