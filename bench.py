@@ -144,6 +144,7 @@ def run_ours(args) -> dict:
             wk.graph.replay()
     else:
         for _ in range(K):
+            wk._pre()
             wk.engine.forward_backward()
             wk._exchange()
             if cfg.mode == "sync":
@@ -179,7 +180,7 @@ def run_ours(args) -> dict:
 
     err = job.ps.error_bits()
     value = K * B * world / (ms_dev / 1e3)
-    ps_launches = 3 if cfg.mode == "sync" else 4
+    ps_launches = (8 if wk.overlap_pull else 3) if cfg.mode == "sync" else 4
     kernels = getattr(wk.engine, "kernels_per_step", 0)
     out = {
         "metric": "ResNet-18 images/sec (%s mode, parameter server)" % cfg.mode,

@@ -25,7 +25,9 @@ if mode == "sync":
     # oracle for the FIRST step: mean over ranks of the fp16-rounded local gradients, applied to the initial master
     w0 = job.ps.gather_master().clone()
     job.worker.engine.load_batch(xs[0], ys[0])
+    hook, job.worker.engine.seg_wait = job.worker.engine.seg_wait, None     # oracle pass: compute only, no pull waits
     job.worker.engine.forward_backward()
+    job.worker.engine.seg_wait = hook
     torch.cuda.synchronize()
     g_local = job.ps.grad[rank].clone().half().float()
     job.ps.grad[rank].zero_()
@@ -42,6 +44,13 @@ for i in range(steps):
         extra["max_abs_diff_vs_single_process_mean_step"] = float((got - want).abs().max())
 job.worker.drain()
 job.barrier()
+if job.worker.overlap_pull:
+    # the last update is normally pulled at the start of the next step: run that segmented pull now
+    job.ps.pull_segments()
+    for k in range(job.ps.nseg):
+        job.ps.wait_segment(k)
+    torch.cuda.synchronize()
+    job.barrier()
 master = job.ps.gather_master()
 mine = job.ps.wbf16[rank].clone()
 if mode == "async":

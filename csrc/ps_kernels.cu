@@ -209,6 +209,60 @@ __global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__
   }
 }
 
+// Segmented PULL: the arena is in forward order, so the owner broadcasts it front to back in `nseg` layer groups
+// and bumps a per-group delivery counter on every worker after each group.  The next forward pass waits per group
+// (wait_seg_kernel in front of the group's first conv), so the pull overlaps the forward pass layer group by layer
+// group instead of preceding it.  seg[] holds nseg+1 LOCAL element offsets (multiples of 8) into the shard.
+struct SegBounds {
+  long long off[DPS_MAX_SEGS + 1];
+  int nseg;
+};
+__global__ void __launch_bounds__(256) pull_seg_kernel(const __grid_constant__ DpsTables T,
+                                                       const __grid_constant__ SegBounds sb) {
+  const int W = T.world, BS = T.block_elems;
+  const long long n_small = T.n_small;
+  const int G = gridDim.x, b = blockIdx.x;
+  for (int sg = 0; sg < sb.nseg; ++sg) {
+    const long long s0 = sb.off[sg], s1 = sb.off[sg + 1];
+    const long long per = (((s1 - s0) / VEC + G - 1) / G) * VEC;
+    const long long lo = s0 + (long long)b * per, hi = min(s1, lo + per);
+    for (int o = T.rank_lo; o < T.rank_hi; ++o) {
+      const float* master = T.master[o];
+      for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
+        const long long g = global_index(l, o, W, BS);
+        const F8 p = load_f32x8(master + l);
+        const uint4 h = to_bf16x8(p);
+        for (int ww = 0; ww < W; ++ww) {
+          const int w = (o + ww) % W;
+          st_v4(T.wbf16[w] + g, h);
+          if (g < n_small) store_f32x8(T.small[w] + g, p);
+        }
+      }
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        __threadfence_system();
+        for (int w = 0; w < W; ++w) red_relaxed_sys_add(T.flags[w] + DPS_F_SEGCOUNT + sg, 1u);
+      }
+      __syncthreads();
+    }
+  }
+}
+
+__global__ void wait_seg_kernel(const __grid_constant__ DpsTables T, int rank, int seg, uint32_t step_arg,
+                                uint32_t ctas_per_owner, unsigned long long timeout_ns) {
+  if (threadIdx.x == 0) {
+    const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
+    const uint32_t target = (step + 1) * ctas_per_owner * (uint32_t)T.world;
+    if (!wait_ge(T.flags[rank] + DPS_F_SEGCOUNT + seg, target, timeout_ns))
+      atomicOr(T.flags[rank] + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
+  }
+}
+
+// Last kernel of a round when the pull runs at the START of the step: advance the device-resident round counter.
+__global__ void bump_step_kernel(const __grid_constant__ DpsTables T) {
+  if (threadIdx.x == 0 && blockIdx.x == 0 && T.step_ctr) T.step_ctr[0] += 1;
+}
+
 // Worker side of the pull: block the stream until all W owners have delivered `step`.
 __global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, uint32_t step_arg,
                                  uint32_t ctas_per_owner, unsigned long long timeout_ns, int bump) {
@@ -477,6 +531,36 @@ DPS_API int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_
                           unsigned long long timeout_ns, int bump, void* stream) {
   if (int e = check_tables(T)) return e;
   wait_pull_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, rank, step, (uint32_t)ctas_per_owner, timeout_ns, bump);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_pull_segments(const DpsTables* T, const long long* seg_offsets, int nseg, int ctas, void* stream) {
+  if (int e = check_tables(T)) return e;
+  if (nseg < 1 || nseg > DPS_MAX_SEGS) DPS_FAIL(1, "nseg out of range");
+  SegBounds sb;
+  sb.nseg = nseg;
+  for (int i = 0; i <= nseg; ++i) {
+    sb.off[i] = seg_offsets[i];
+    if (sb.off[i] % 8 || sb.off[i] < 0 || sb.off[i] > T->shard_elems || (i && sb.off[i] < sb.off[i - 1]))
+      DPS_FAIL(1, "bad segment offset %lld", (long long)sb.off[i]);
+  }
+  pull_seg_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, sb);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_wait_segment(const DpsTables* T, int rank, int seg, unsigned step, int ctas_per_owner,
+                             unsigned long long timeout_ns, void* stream) {
+  if (int e = check_tables(T)) return e;
+  wait_seg_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, rank, seg, step, (uint32_t)ctas_per_owner, timeout_ns);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_bump_step(const DpsTables* T, void* stream) {
+  if (int e = check_tables(T)) return e;
+  bump_step_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

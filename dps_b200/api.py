@@ -214,11 +214,37 @@ class Worker:
                                       self.ps.grad[self.rank], job.model_cpu, batch=self.cfg.batch_size,
                                       image_size=self.cfg.image_size, device=job.device)
         self._accum = 0
+        if self.overlap_pull:
+            self._side = torch.cuda.Stream(device=job.device)
+            self.ps.set_segments(self.engine.segment_boundaries)
+            self.engine.seg_wait = lambda k: self.ps.wait_segment(k)
+            self._weights_stale = False
 
     # ------------------------------------------------------------------ the step
+    @property
+    def overlap_pull(self) -> bool:
+        """Sync mode, native engine: the pull of update t runs at the START of step t+1 on a side stream, layer
+        group by layer group, and the forward pass waits per group (BASELINE north star: pull overlapped with the
+        next forward pass)."""
+        return (self.cfg.overlap_pull and self.cfg.mode == "sync" and self.engine_kind == "native"
+                and self.cfg.sync_steps == 1)
+
+    def _pre(self) -> None:
+        """Start of a step: fork the segmented pull onto the side stream."""
+        if not self.overlap_pull:
+            return
+        cur = torch.cuda.current_stream()
+        self._side.wait_stream(cur)
+        with torch.cuda.stream(self._side):
+            self.ps.pull_segments()
+
     def _exchange(self) -> None:
         """Everything after backward: push -> (barrier, reduce, SGD | ring, staleness apply) -> pull."""
-        if self.cfg.mode == "sync":
+        if self.overlap_pull:
+            self.ps.push_sync()
+            self.ps.bump_step()
+            torch.cuda.current_stream().wait_stream(self._side)      # join the pull branch
+        elif self.cfg.mode == "sync":
             self.ps.push_sync()
             self.ps.pull()
         else:
@@ -229,7 +255,7 @@ class Worker:
     def _build_graph(self) -> None:
         self.ps.use_device_counters(True)
         saved = {k: v.clone() for k, v in self.engine.bn_buffers().items()}   # warm-up must not count as a step
-        self.engine.capture(extra=self._exchange if self.cfg.sync_steps == 1 else None)
+        self.engine.capture(extra=self._exchange if self.cfg.sync_steps == 1 else None, pre=self._pre)
         for k, v in self.engine.bn_buffers().items():
             v.copy_(saved[k])
         # capture ran one eager warm-up step on the engine only: clear what it accumulated
@@ -247,6 +273,7 @@ class Worker:
         if use_graph:
             self.graph.replay()
         else:
+            self._pre()
             self.engine.forward_backward()
         self._accum += 1
         if self._accum >= self.cfg.sync_steps:
@@ -297,6 +324,8 @@ class Worker:
                  shard: bool = False) -> float:
         """Top-1 accuracy in percent with running BN statistics (reference: worker.py:313-331).
         shard=True evaluates batches rank::world and all-reduces the counts (SURVEY Q14)."""
+        if self.overlap_pull and self.local_step_counter > 0:
+            self.ps.refresh_weights(self.job.group)     # the last update is pulled at the start of the NEXT step
         correct = total = 0
         B = self.cfg.batch_size
         for i, (x, y) in enumerate(loader):

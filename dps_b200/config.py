@@ -65,6 +65,7 @@ class Config:
     device: str = "auto"                  # 'auto' | 'cpu' | 'cuda'
     engine: str = "native"                # 'native' (sm_100a kernels) | 'torch' (ATen/cuDNN)
     use_cuda_graph: bool = True
+    overlap_pull: bool = True             # sync mode: pull at step start, overlapped with forward per layer group
     async_ring_slots: int = 4             # ring depth per (owner, worker) pair
     # ---- outputs -----------------------------------------------------------
     metrics_dir: Optional[str] = None     # write METRICS_JSON records to files here

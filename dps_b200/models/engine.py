@@ -80,6 +80,7 @@ class ResNetEngine:
         self._scratch_slices: List[Tuple[int, int]] = []
         self._build()
         self.graph: Optional[torch.cuda.CUDAGraph] = None
+        self.seg_wait: Optional[Callable[[int], None]] = None   # set by the worker: wait for a pulled layer group
 
     # ------------------------------------------------------------------ helpers
     def _bf(self, *shape) -> torch.Tensor:
@@ -203,8 +204,20 @@ class ResNetEngine:
                                  "stem_im2col")
         self.fwd.append(im2col)
         self.evalf.append(im2col)
+        # layer groups of the segmented pull: [small params + stem + layer1 | layer2 | layer3 | layer4 | fc]
+        self.segment_boundaries = [0] + [self.layout.entries[n].offset for n in
+                                         ("layer2.0.conv1.weight", "layer3.0.conv1.weight", "layer4.0.conv1.weight",
+                                          "fc.weight")] + [self.layout.total]
+        first_of_group = {id(stem): 0}
+        for bi, blk in enumerate(blocks):
+            if bi > 0 and bi % BLOCKS_PER_STAGE == 0:
+                first_of_group[id(blk["u1"])] = bi // BLOCKS_PER_STAGE
         for u in units:
+            if id(u) in first_of_group:
+                k = first_of_group[id(u)]
+                self.fwd.append(lambda k=k: self.seg_wait(k) if self.seg_wait is not None else None)
             self._finalize_unit_fwd(u)
+        self.fwd.append(lambda: self.seg_wait(4) if self.seg_wait is not None else None)
 
         # head
         HW = self.featH * self.featH
@@ -319,17 +332,22 @@ class ResNetEngine:
         for f in self.evalf:
             f()
 
-    def capture(self, extra: Optional[Callable[[], None]] = None, warmup: int = 1) -> None:
-        """Capture forward+backward (+ `extra`, e.g. push/pull) into one CUDA graph."""
+    def capture(self, extra: Optional[Callable[[], None]] = None, warmup: int = 1,
+                pre: Optional[Callable[[], None]] = None) -> None:
+        """Capture [pre] + forward + backward + [extra] (e.g. pull fork / push + join) into one CUDA graph."""
         s = torch.cuda.Stream(device=self.dev)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
+            saved, self.seg_wait = self.seg_wait, None       # the warm-up pass is compute only
             for _ in range(warmup):
                 self.forward_backward()
+            self.seg_wait = saved
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
         g = torch.cuda.CUDAGraph()
         with torch.cuda.graph(g):
+            if pre is not None:
+                pre()
             self.forward_backward()
             if extra is not None:
                 extra()

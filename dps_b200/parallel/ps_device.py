@@ -166,6 +166,43 @@ class DevicePS:
                                                int(self.device_counters), L.stream_ptr(stream)), "wait_pull")
                 self.launches += 1
 
+    # ---- segmented pull (overlaps the next forward pass) ----------------------------------
+    def set_segments(self, global_boundaries) -> None:
+        """global_boundaries: increasing arena element offsets [0, ..., total]; each is rounded UP to a multiple of
+        W*block (so a layer group is fully inside its segment) and converted to local shard offsets."""
+        q = self.world * self.layout.block_elems
+        loc = []
+        for g in global_boundaries:
+            g = min(self.total, (int(g) + q - 1) // q * q)
+            loc.append(g // self.world)
+        loc[0], loc[-1] = 0, self.E
+        for i in range(1, len(loc)):
+            loc[i] = max(loc[i], loc[i - 1])
+        self.nseg = len(loc) - 1
+        self._seg = (C.c_longlong * len(loc))(*loc)
+
+    def pull_segments(self, stream=None) -> None:
+        L.check(self.lib.dps_pull_segments(self._tp, self._seg, self.nseg, self.ctas, L.stream_ptr(stream)),
+                "pull_segments")
+        self.launches += 1
+
+    def wait_segment(self, seg: int, stream=None, rank: Optional[int] = None) -> None:
+        r = self.rank if rank is None else rank
+        L.check(self.lib.dps_wait_segment(self._tp, r, seg, self.step, self.ctas, self.timeout_ns,
+                                          L.stream_ptr(stream)), "wait_segment")
+        self.launches += 1
+
+    def bump_step(self, stream=None) -> None:
+        L.check(self.lib.dps_bump_step(self._tp, L.stream_ptr(stream)), "bump_step")
+        self.launches += 1
+
+    def refresh_weights(self, group=None) -> None:
+        """Bring the local bf16 replica up to date with the master outside the step (evaluation / shutdown)."""
+        flat = self.gather_master(group)
+        for r in self.local:
+            self.wbf16[r].copy_(flat.to(torch.bfloat16))
+            self.small[r].copy_(flat[: self.n_small])
+
     def sync_round(self, lr: Optional[float] = None, stream=None) -> None:
         """push -> (barrier, reduce, SGD) -> pull -> wait; advances the round counter."""
         self.push_sync(lr, stream)

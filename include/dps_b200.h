@@ -45,6 +45,8 @@ extern "C" {
 #define DPS_F_TICKET 704        /* [32][2] local {tag, ticket} per owner                         */
 #define DPS_F_SEEN 800          /* [32] version of each shard at this worker's last pull         */
 #define DPS_F_DROP 832          /* [32] local: this step's push to owner o was skipped            */
+#define DPS_F_SEGCOUNT 864      /* [16] segmented pull: deliveries received per layer group           */
+#define DPS_MAX_SEGS 16
 #define DPS_FLAG_WORDS 1024
 
 #define DPS_ERR_BARRIER_TIMEOUT 1u
@@ -100,6 +102,12 @@ int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, f
 int dps_pull_bcast(const DpsTables* T, unsigned step, int ctas, void* stream);
 int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_per_owner, unsigned long long timeout_ns,
                   int bump, void* stream);
+/* Segmented pull (layer groups in forward order) + per-group wait: overlaps the pull with the next forward pass.
+ * seg_offsets: nseg+1 LOCAL shard offsets (multiples of 8).  dps_bump_step advances the device round counter. */
+int dps_pull_segments(const DpsTables* T, const long long* seg_offsets, int nseg, int ctas, void* stream);
+int dps_wait_segment(const DpsTables* T, int rank, int seg, unsigned step, int ctas_per_owner,
+                     unsigned long long timeout_ns, void* stream);
+int dps_bump_step(const DpsTables* T, void* stream);
 /* reference: server.py:290-304,171-186 (async apply-on-arrival with staleness weighting) */
 int dps_push_async(const DpsTables* T, int rank, unsigned step, int ctas, unsigned long long timeout_ns,
                    void* stream);
