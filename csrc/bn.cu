@@ -60,13 +60,13 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
     const float sc = gamma[c] * rstd;
     s_scale[c] = sc;
     s_shift[c] = beta[c] - mean * sc;
-    if (training && blockIdx.x == 0) {
+    if (training && (c % gridDim.x) == blockIdx.x) {    // spread over the grid: no single CTA is delayed by it
       save_mean[c] = mean;
       save_rstd[c] = rstd;
       const float unbiased = var * (float)P / (float)max(1LL, P - 1);
       running_mean[c] = (1.f - momentum) * running_mean[c] + momentum * mean;
       running_var[c] = (1.f - momentum) * running_var[c] + momentum * unbiased;
-      if (c == 0) *num_batches += 1;
+      if (c == 0) *num_batches += 1;     // channel 0 is owned by CTA 0 only
     }
   }
   __syncthreads();
@@ -191,7 +191,7 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
     s_a[c] = gr;
     s_b[c] = -k;
     s_c[c] = -gr * sdz * invP + k * mean[c];
-    if (blockIdx.x == 0) {
+    if ((c % gridDim.x) == blockIdx.x) {
       dgamma[c] += sdzx;
       dbeta[c] += sdz;
     }
@@ -231,8 +231,10 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
 using namespace dps;
 
 static int bn_grid(long long nvec) {
-  long long want = (nvec + kBnThreads - 1) / kBnThreads;
-  long long cap = 148 * 3;      // exactly one wave at 3 CTAs / SM (77-80 registers): no partial last wave
+  // at least 4 vectors (one unrolled batch) per thread: small layers use few CTAs, every CTA repeats the prologue
+  long long want = (nvec + 4 * kBnThreads - 1) / (4 * kBnThreads);
+  static const int per_sm = [] { const char* e = getenv("DPS_BN_CTAS_PER_SM"); return e ? atoi(e) : 3; }();
+  long long cap = 148 * per_sm;  // default: exactly one wave at 3 CTAs / SM (77-80 registers), no partial last wave
   return (int)(want < cap ? (want < 1 ? 1 : want) : cap);
 }
 

@@ -298,7 +298,11 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
   if (tmem_empty != nullptr) asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");   // staging is reused by the next tile
 }
 
-template <int BLOCK_N, bool B_MN>
+// CL > 1: the CL CTAs of a cluster compute CL adjacent N tiles of the SAME pixel tile, so they need the same
+// activation box.  Each CTA fetches 1/CL of its rows and TMA-multicasts them into all CL CTAs (L2->SM activation
+// traffic / CL); the weight tile stays private.  A stage may be refilled only after ALL CL consumers released it:
+// every MMA thread multicasts its tcgen05.commit to the `empty` barrier of all CTAs (barrier count = CL).
+template <int BLOCK_N, bool B_MN, int CL>
 __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant__ CUtensorMap tmA,
                                                            const __grid_constant__ CUtensorMap tmB,
                                                            const __grid_constant__ ConvParams p) {
@@ -331,7 +335,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   }
   if (warp == 1) {
     if (elect_one()) {
-      for (int s = 0; s < nst; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      for (int s = 0; s < nst; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], CL); }
       mbar_init(tmem_full, 1);
       fence_barrier_init();
     }
@@ -341,9 +345,11 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
   }
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();          // peers' barriers are initialised before anyone signals them
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   pdl_wait();            // prologue above overlapped the previous kernel's tail; dependent data from here on
+  constexpr uint16_t kClusterMask = (uint16_t)((1u << CL) - 1u);
 
   if (warp == 0) {
     // ===================== TMA producer =====================
@@ -356,7 +362,16 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
         uint8_t* a = stages + s * S::kStageBytes;
         uint8_t* b = a + kABytes;
         mbar_expect_tx(&full[s], S::kStageBytes);
-        tma_load_5d(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
+        if (CL == 1) {
+          tma_load_5d(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
+        } else {
+          // my 128/CL rows of the box (tile order: w fastest, then h, then n), multicast to the whole cluster
+          const int q = (int)cluster_ctarank();
+          const int base = (q * (kTileM / CL)) >> p.bw_sh;          // first (h, n) line of my slice
+          const int bh_sh = p.bhw_sh - p.bw_sh;
+          tma_load_5d_mc(a + q * (kTileM / CL) * 128, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph,
+                         h0 + tp.da + (base & ((1 << bh_sh) - 1)), n0 + (base >> bh_sh), kClusterMask);
+        }
         if (!B_MN) {
           tma_load_2d(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0);
         } else {
@@ -385,7 +400,8 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
           const uint64_t bd = bdesc + (uint64_t)(B_MN ? k * 128 : k * 2);
           umma_bf16(tmem_base, ad, bd, idesc, (kb | k) != 0 ? 1u : 0u);
         }
-        umma_commit(&empty[s]);            // smem slot free once these MMAs have read it
+        if (CL == 1) umma_commit(&empty[s]);            // smem slot free once these MMAs have read it
+        else umma_commit_mc(&empty[s], kClusterMask);   // ... in every CTA of the cluster
       }
       umma_commit(tmem_full);              // accumulator complete
     }
@@ -396,6 +412,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
 
   tc_fence_before();
   __syncthreads();
+  if (CL > 1) cluster_sync_all();          // nobody leaves while peers may still multicast into / signal this CTA
   if (warp == 1) {
     tc_fence_after();
     tmem_dealloc(tmem_base, BLOCK_N);
@@ -915,6 +932,7 @@ struct ConvPlan {
   int block_n;
   bool b_mn;
   bool halo;                      // persistent halo kernel (layer1-type convs)
+  int cluster;                    // CTAs per cluster along N (activation multicast); 1 = none
   CUtensorMap tmA, tmB;
   ConvParams cp;
   WgradParams wp;
@@ -924,16 +942,17 @@ struct ConvPlan {
   size_t smem;
 };
 
-template <int BN_, bool MN_>
+template <int BN_, bool MN_, int CL_ = 1>
 static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
-  auto kern = tapconv_kernel<BN_, MN_>;
+  auto kern = tapconv_kernel<BN_, MN_, CL_>;
   static bool configured = false;
   if (!configured) {
     DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    ConvSmem<BN_>::total(kMaxStages)));
     configured = true;
   }
-  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, pl.tmA, pl.tmB, pl.cp));
+  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, dim3(1, CL_, 1),
+                               pl.tmA, pl.tmB, pl.cp));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
@@ -1008,6 +1027,14 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     const long long tiles = (long long)N * Ho * Wo / kTileM;
     const int groups = (kind == 1 && stride == 2 && R == 3) ? 4 : 1;
     if (pl->block_n == 128 && tiles * (ngemm / 128) * groups < 100) pl->block_n = 64;
+    // wide layers: 64-wide N tiles in clusters of 4 (or 2) that share the activation box by TMA multicast
+    pl->cluster = 1;
+    const char* e = getenv("DPS_CLUSTER");
+    if (!(e && e[0] == '0') && ngemm >= 256) {
+      pl->block_n = 64;
+      const int ny = ngemm / 64;
+      pl->cluster = (ny % 4 == 0) ? 4 : (ny % 2 == 0 ? 2 : 1);
+    }
   }
   pl->b_mn = (kind == 1);
   ConvParams& cp = pl->cp;
@@ -1026,6 +1053,12 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     delete pl;
     DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
   }
+  if (pl->halo) pl->cluster = 1;
+  while (pl->cluster > 1 && (kTileM / pl->cluster) % cp.BW != 0) pl->cluster /= 2;   // a slice is whole box lines
+  // each CTA of a cluster loads 128/cluster rows of the box: sub-box = BW x sub_bh x sub_bn
+  const int lines = kTileM / pl->cluster / cp.BW;
+  const int sub_bh = lines < cp.BH ? lines : cp.BH;
+  const int sub_bn = lines / sub_bh;
   for (cp.bw_sh = 0; (1 << cp.bw_sh) < cp.BW; ++cp.bw_sh) {}
   for (cp.bhw_sh = 0; (1 << cp.bhw_sh) < cp.BW * cp.BH; ++cp.bhw_sh) {}
   cp.tiles_w = TW / cp.BW;
@@ -1055,8 +1088,8 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         cp.taps[0][nt++] = t;
       }
     cp.ntaps[0] = nt;
-    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (pl->halo ? 2 : 0), cp.BH + (pl->halo ? 2 : 0),
-                      cp.BN);
+    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (pl->halo ? 2 : 0), sub_bh + (pl->halo ? 2 : 0),
+                      sub_bn);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->block_n);
   } else {
     cp.out_H = H; cp.out_W = W; cp.out_C = Cin; cp.os = stride;
@@ -1093,8 +1126,8 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         }
       cp.ngroups = g;
     }
-    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW + (pl->halo ? 2 : 0), cp.BH + (pl->halo ? 2 : 0),
-                      cp.BN);
+    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW + (pl->halo ? 2 : 0), sub_bh + (pl->halo ? 2 : 0),
+                      sub_bn);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, 64);
   }
   if (rc) { delete pl; return rc; }
@@ -1230,6 +1263,10 @@ DPS_API int dps_conv_plan_run(void* plan, void* stream) {
   if (pl->kind == 2 && pl->whalo) return launch_wgrad_halo(*pl, st);
   if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
   if (pl->halo) return pl->b_mn ? launch_halo<true>(*pl, st) : launch_halo<false>(*pl, st);
+  if (pl->block_n == 64 && pl->cluster == 4)
+    return pl->b_mn ? launch_tapconv<64, true, 4>(*pl, st) : launch_tapconv<64, false, 4>(*pl, st);
+  if (pl->block_n == 64 && pl->cluster == 2)
+    return pl->b_mn ? launch_tapconv<64, true, 2>(*pl, st) : launch_tapconv<64, false, 2>(*pl, st);
   if (pl->b_mn) return pl->block_n == 128 ? launch_tapconv<128, true>(*pl, st) : launch_tapconv<64, true>(*pl, st);
   return pl->block_n == 128 ? launch_tapconv<128, false>(*pl, st) : launch_tapconv<64, false>(*pl, st);
 }

@@ -13,7 +13,7 @@
 
 namespace dps {
 
-constexpr int kHeadThreads = 256;
+constexpr int kHeadThreads = 512;
 constexpr int kMaxFeat = 512;
 constexpr int kMaxClasses = 128;
 
@@ -163,11 +163,12 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
                                                           int N, int H, int W) {
   pdl_launch_dependents();
   pdl_wait();
-  const long long total = (long long)N * H * W * 8;        // 8 vectors of 8 columns per pixel
+  // only columns 0..31 are written (27 valid + 5 zeros); columns 32..63 of the buffer are zero from allocation
+  const long long total = (long long)N * H * W * 4;        // 4 vectors of 8 columns per pixel
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < total;
        i += (long long)gridDim.x * blockDim.x) {
-    const int vec = (int)(i & 7);
-    long long pix = i >> 3;
+    const int vec = (int)(i & 3);
+    long long pix = i >> 2;
     const int x = (int)(pix % W);
     const int y = (int)((pix / W) % H);
     const int n = (int)(pix / ((long long)W * H));
@@ -179,11 +180,11 @@ __global__ void __launch_bounds__(256) stem_im2col_kernel(const float* __restric
       if (k < 27) {
         const int c = k % 3, s = (k / 3) % 3, r = k / 9;
         const int iy = y + r - 1, ix = x + s - 1;
-        if (iy >= 0 && iy < H && ix >= 0 && ix < W) val = img[(((size_t)n * 3 + c) * H + iy) * W + ix];
+        if (iy >= 0 && iy < H && ix >= 0 && ix < W) val = __ldg(img + (((size_t)n * 3 + c) * H + iy) * W + ix);
       }
       v[e] = val;
     }
-    st_v4(col + i * 8, make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+    st_v4(col + pix * 64 + vec * 8, make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
                                   pack_bf16x2(v[6], v[7])));
   }
 }
@@ -209,7 +210,7 @@ DPS_API int dps_head_forward_backward(const void* act, const void* w, const floa
 }
 
 DPS_API int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* stream) {
-  const long long total = (long long)N * H * W * 8;
+  const long long total = (long long)N * H * W * 4;
   const int grid = (int)((total + 255) / 256 < 148 * 8 ? (total + 255) / 256 : 148 * 8);
   // first kernel of a step: its predecessor is a memset / H2D copy node, so it is launched without the
   // programmatic-dependency attribute (griddepcontrol.wait in the kernel is then a no-op)

@@ -258,3 +258,31 @@ def test_async_push_is_wait_free_when_the_ring_is_full():
     st = ps.async_stats(0)
     assert st["async_updates"] == 2
     ps.close()
+
+
+def test_segmented_pull_delivers_layer_groups_in_order():
+    """Pull overlapped with forward: five layer groups, per-group delivery counters, same bytes as the plain pull."""
+    from dps_b200.ops import _lib as L
+    W = 4
+    model, layout, ps, flat0 = _setup(W, mode="sync", lr=0.1)
+    bounds = [0] + [layout.entries[n].offset for n in ("layer2.0.conv1.weight", "layer3.0.conv1.weight",
+                                                        "layer4.0.conv1.weight", "fc.weight")] + [layout.total]
+    ps.set_segments(bounds)
+    assert ps.nseg == 5
+    new = torch.randn(layout.total, device="cuda")
+    sh = layout.to_shards(new)
+    for r in range(W):
+        ps.master[r].copy_(sh[r])
+        ps.wbf16[r].zero_()
+    ps.pull_segments()
+    for r in range(W):
+        for k in range(ps.nseg):
+            ps.wait_segment(k, rank=r)
+    torch.cuda.synchronize()
+    for r in range(W):
+        assert torch.equal(ps.wbf16[r], new.to(torch.bfloat16))
+        assert torch.equal(ps.small[r], new[: layout.n_small])
+        counts = ps.flag_words(r)[L.F_SEGCOUNT:L.F_SEGCOUNT + 5].tolist()
+        assert counts == [W * ps.ctas] * 5
+    assert ps.error_bits(0) == 0
+    ps.close()
