@@ -420,6 +420,115 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
 }
 
 // ------------------------------------------------------------------------------------------
+// pairconv_kernel: tapconv on CTA PAIRS (tcgen05 cta_group::2), 256 pixels x 128 channels per pair.
+//
+// The two CTAs of a cluster sit on the two SMs of a TPC.  Each loads the activation box of ITS 128-pixel tile and
+// only HALF of the 128-wide weight tile (64 rows / columns); one thread of the leader CTA issues
+// tcgen05.mma.cta_group::2 (M = 256), which reads A and the two B halves from both CTAs' shared memory and writes
+// rows 0..127 / 128..255 of the accumulator into the TMEM of CTA 0 / CTA 1.  Per SM and reduction block that is
+// 16 KB + 8 KB instead of 16 KB + 16 KB: L2->SM traffic -- the bound of these layers (profiles/launches_v5) --
+// drops by a quarter against 128x128 tiles and by half against 128x64 tiles.
+// Protocol: both producers wait on their own `empty` barrier and signal bytes on the LEADER's `full` barrier
+// (peer bit cleared); the leader arms it with the bytes of both CTAs; tcgen05.commit.cta_group::2 multicasts the
+// release of a stage (and the accumulator-ready signal) to both CTAs.
+// ------------------------------------------------------------------------------------------
+constexpr int kPairN = 128;
+constexpr int kPairStage = kABytes + 64 * kKBlock * 2;      // 16 KiB activations + 8 KiB half weight tile
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kThreads) pairconv_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                            const __grid_constant__ CUtensorMap tmB,
+                                                            const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  const int nst = p.nstages;
+  uint8_t* stages = smem;
+  uint64_t* full = reinterpret_cast<uint64_t*>(smem + nst * kPairStage);
+  uint64_t* empty = full + kMaxStages;
+  uint64_t* tmem_full = empty + kMaxStages;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tmem_full + 1);
+
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  const int grp = blockIdx.z;
+  const int nkb = p.ntaps[grp] * p.red_blocks;
+  const int rank = (int)cluster_ctarank();               // 0 = leader (issues the MMAs)
+
+  int t = blockIdx.x;                                    // consecutive pixel tiles form a pair
+  const int tw = t % p.tiles_w; t /= p.tiles_w;
+  const int th = t % p.tiles_h; t /= p.tiles_h;
+  const int w0 = tw * p.BW, h0 = th * p.BH, n0 = t * p.BN;
+  const int c_out0 = blockIdx.y * kPairN;
+
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      for (int s = 0; s < nst; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+      mbar_init(tmem_full, 1);
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc_2sm(tmem_slot, kPairN);                   // same warp id in both CTAs, same destination address
+    tmem_relinquish_2sm();
+  }
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                    // both CTAs' barriers and TMEM are ready
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  if (warp == 0) {
+    if (elect_one()) {
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % nst, ph = (kb / nst) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        const Tap tp = p.taps[grp][kb / p.red_blocks];
+        const int cb = kb % p.red_blocks;
+        uint8_t* a = stages + s * kPairStage;
+        uint8_t* b = a + kABytes;
+        if (rank == 0) mbar_expect_tx(&full[s], 2 * kPairStage);        // bytes of BOTH CTAs land on my barrier
+        tma_load_5d_2sm(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
+        if (!B_MN) tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0 + rank * 64);
+        else       tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + c_out0 + rank * 64, cb * kKBlock);
+      }
+    }
+  } else if (warp == 1) {
+    if (rank == 0 && elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(256, kPairN, 0, B_MN ? 1 : 0);
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % nst, ph = (kb / nst) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_addr = smem_u32(stages + s * kPairStage);
+        const uint32_t b_addr = a_addr + kABytes;
+        const uint64_t adesc = make_smem_desc(a_addr, 16, 1024);
+        const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+        for (int k = 0; k < kKBlock / 16; ++k)
+          umma_bf16_2sm(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(B_MN ? k * 128 : k * 2), idesc,
+                        (kb | k) != 0 ? 1u : 0u);
+        umma_commit_2sm(&empty[s], 3);       // stage free in both CTAs once these MMAs have read it
+      }
+      umma_commit_2sm(tmem_full, 3);         // accumulators of both CTAs complete
+    }
+  } else {
+    conv_epilogue<kPairN, 4>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  cluster_sync_all();                                    // the peer may still be reading / signalling
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc_2sm(tmem_base, kPairN);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
 // haloconv_kernel: 3x3 stride-1 convolutions with 64 reduction channels and 64 output channels (layer1 fprop
 // and dgrad), persistent, weights resident.
 //
@@ -933,6 +1042,7 @@ struct ConvPlan {
   bool b_mn;
   bool halo;                      // persistent halo kernel (layer1-type convs)
   int cluster;                    // CTAs per cluster along N (activation multicast); 1 = none
+  bool pair;                      // pairconv_kernel (cta_group::2)
   CUtensorMap tmA, tmB;
   ConvParams cp;
   WgradParams wp;
@@ -954,6 +1064,20 @@ static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
   DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, dim3(1, CL_, 1),
                                pl.tmA, pl.tmB, pl.cp));
   DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+template <bool MN_>
+static int launch_pair(const ConvPlan& pl, cudaStream_t st) {
+  auto kern = pairconv_kernel<MN_>;
+  static bool configured = false;
+  const int smem_max = 1024 + kMaxStages * kPairStage + kCtrlBytes;
+  if (!configured) {
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
+    configured = true;
+  }
+  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(kThreads), 1024 + pl.cp.nstages * kPairStage + kCtrlBytes, st,
+                               dim3(2, 1, 1), pl.tmA, pl.tmB, pl.cp));
   return 0;
 }
 
@@ -1027,10 +1151,19 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     const long long tiles = (long long)N * Ho * Wo / kTileM;
     const int groups = (kind == 1 && stride == 2 && R == 3) ? 4 : 1;
     if (pl->block_n == 128 && tiles * (ngemm / 128) * groups < 100) pl->block_n = 64;
+    // CTA pairs (cta_group::2): 256 x 128 pair tiles when N is a multiple of 128 and the pixel tiles pair up
+    pl->pair = false;
+    {
+      const char* ep = getenv("DPS_PAIR");
+      // measured: neutral for the 256/512-wide layers, slightly slower than plain 128x128 tiles at N = 128
+      if (!(ep && ep[0] == '0') && ngemm % 128 == 0 && ngemm >= 256 && tiles % 2 == 0) pl->pair = true;
+    }
     // wide layers: 64-wide N tiles in clusters of 4 (or 2) that share the activation box by TMA multicast
     pl->cluster = 1;
     const char* e = getenv("DPS_CLUSTER");
-    if (!(e && e[0] == '0') && ngemm >= 256) {
+    if (pl->pair) {
+      pl->block_n = 128;
+    } else if (!(e && e[0] == '0') && ngemm >= 256) {
       pl->block_n = 64;
       const int ny = ngemm / 64;
       pl->cluster = (ny % 4 == 0) ? 4 : (ny % 2 == 0 ? 2 : 1);
@@ -1053,7 +1186,7 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     delete pl;
     DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
   }
-  if (pl->halo) pl->cluster = 1;
+  if (pl->halo) { pl->cluster = 1; pl->pair = false; }
   while (pl->cluster > 1 && (kTileM / pl->cluster) % cp.BW != 0) pl->cluster /= 2;   // a slice is whole box lines
   // each CTA of a cluster loads 128/cluster rows of the box: sub-box = BW x sub_bh x sub_bn
   const int lines = kTileM / pl->cluster / cp.BW;
@@ -1090,7 +1223,7 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     cp.ntaps[0] = nt;
     rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (pl->halo ? 2 : 0), sub_bh + (pl->halo ? 2 : 0),
                       sub_bn);
-    if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->block_n);
+    if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->pair ? 64 : pl->block_n);  // pair: half tile per CTA
   } else {
     cp.out_H = H; cp.out_W = W; cp.out_C = Cin; cp.os = stride;
     if (stride == 1) {
@@ -1133,6 +1266,10 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   if (rc) { delete pl; return rc; }
   pl->grid = dim3(cp.tiles_w * cp.tiles_h * tiles_n, ngemm / pl->block_n, cp.ngroups);
   cp.nstages = ((long long)pl->grid.x * pl->grid.y * pl->grid.z <= 148) ? kMaxStages : kMinStages;
+  if (pl->pair) {
+    const long long ctas = (long long)pl->grid.x * pl->grid.y * pl->grid.z;
+    cp.nstages = ctas <= 148 ? kMaxStages : 4;          // staging needs >= 3 stages of 24 KiB
+  }
   if (pl->halo) {
     cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
     pl->grid = dim3(cp.tiles_total < 148 ? cp.tiles_total : 148, 1, 1);      // persistent: one CTA per SM
@@ -1263,6 +1400,7 @@ DPS_API int dps_conv_plan_run(void* plan, void* stream) {
   if (pl->kind == 2 && pl->whalo) return launch_wgrad_halo(*pl, st);
   if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
   if (pl->halo) return pl->b_mn ? launch_halo<true>(*pl, st) : launch_halo<false>(*pl, st);
+  if (pl->pair) return pl->b_mn ? launch_pair<true>(*pl, st) : launch_pair<false>(*pl, st);
   if (pl->block_n == 64 && pl->cluster == 4)
     return pl->b_mn ? launch_tapconv<64, true, 4>(*pl, st) : launch_tapconv<64, false, 4>(*pl, st);
   if (pl->block_n == 64 && pl->cluster == 2)
