@@ -38,3 +38,15 @@ def test_validation(bad):
 def test_config_roundtrips_into_metrics():
     d = CFG.Config(mode="async", workers=4).to_dict()
     assert d["mode"] == "async" and d["workers"] == 4 and "staleness_bound" in d
+
+
+def test_proto_contract_script_in_sync():
+    """scripts/check_proto.py: ps.proto (human-readable contract) == programmatic descriptors (role of the
+    reference's regenerate_proto.sh:12-16)."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, os.path.join(root, "scripts", "check_proto.py")], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "8 messages, 4 rpcs, OK" in r.stdout

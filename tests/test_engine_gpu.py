@@ -1,5 +1,6 @@
 """the native engine (tcgen05 convs + fused BN/ReLU + fused CE head) vs the reference
 architecture in plain PyTorch fp32 with the same (bf16-rounded) weights: loss and all 62 gradients."""
+import os
 import pytest
 import torch
 
@@ -139,3 +140,22 @@ def test_launcher_one_gpu_end_to_end(tmp_path):
     assert agg["num_workers"] == 1 and agg["total_local_steps"] == 16 and len(agg["accuracy_by_epoch"]) == 2
     assert agg["images_per_second_sum"] > 0 and os.path.exists(ck)
     assert r.stdout.count("METRICS_JSON:") == 2           # one worker record, one server record (Q11)
+
+
+@pytest.mark.gpu
+def test_experiment_pipeline_one_gpu(tmp_path):
+    """dps_b200.experiments: baseline + one sync run -> result file in the reference schema + charts."""
+    import json
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    out = str(tmp_path / "exp")
+    r = subprocess.run([sys.executable, "-m", "dps_b200.experiments", "--workers", "1", "--modes", "sync", "--epochs", "1",
+                        "--train-samples", "1024", "--test-samples", "256", "--out", out, "--master-port", "29731"],
+                       cwd=root, capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-2000:]
+    res = json.load(open(os.path.join(out, "sync_1workers.json")))
+    assert res["server_metrics"]["mode"] == "sync" and res["worker_metrics_aggregated"]["num_workers"] == 1
+    assert res["worker_metrics_aggregated"]["total_local_steps"] == 8
+    assert os.path.exists(os.path.join(out, "charts", "scaling_analysis.png"))
+    assert os.path.exists(os.path.join(out, "baseline", "baseline_summary.json"))
