@@ -345,7 +345,9 @@ class ResNetEngine:
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        # 'relaxed': other threads (the loader's pinned-memory allocations) may call the runtime while this thread
+        # captures; nothing inside the capture allocates.
+        with torch.cuda.graph(g, capture_error_mode="relaxed"):
             if pre is not None:
                 pre()
             self.forward_backward()

@@ -83,8 +83,9 @@ class BatchLoader:
     """
 
     def __init__(self, ds: ArrayDataset, start: int, end: int, batch_size: int, *, train: bool,
-                 seed: int = 0, drop_last: bool = False, pin: bool = False):
+                 seed: int = 0, drop_last: bool = False, pin: bool = False, prefetch: int = 0):
         self.ds, self.start, self.end = ds, start, end
+        self.prefetch = prefetch            # > 0: batches are produced by a background thread, this many ahead
         self.batch_size, self.train, self.drop_last = batch_size, train, drop_last
         self.gen = torch.Generator().manual_seed(seed)
         self.mean = torch.tensor(CIFAR100_MEAN).view(1, 3, 1, 1)
@@ -110,6 +111,45 @@ class BatchLoader:
         return out.permute(0, 3, 1, 2)
 
     def __iter__(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
+        if self.prefetch <= 0:
+            yield from self._batches()
+            return
+        # The reference uses DataLoader(num_workers=2) worker processes (worker.py:181-187); one producer thread is
+        # enough here: the tensor ops release the GIL and a step consumes a batch every ~1.5 ms.
+        import queue
+        import threading
+        q: "queue.Queue" = queue.Queue(maxsize=self.prefetch)
+        stop = threading.Event()
+
+        def produce():
+            try:
+                for b in self._batches():
+                    while not stop.is_set():
+                        try:
+                            q.put(b, timeout=0.1)
+                            break
+                        except queue.Full:
+                            continue
+                    if stop.is_set():
+                        return
+                q.put(None)
+            except BaseException as e:               # surface loader errors in the consumer
+                q.put(e)
+
+        th = threading.Thread(target=produce, daemon=True, name="dps-loader")
+        th.start()
+        try:
+            while True:
+                b = q.get()
+                if b is None:
+                    break
+                if isinstance(b, BaseException):
+                    raise b
+                yield b
+        finally:
+            stop.set()
+
+    def _batches(self) -> Iterator[Tuple[torch.Tensor, torch.Tensor]]:
         n = self.end - self.start
         if n <= 0:
             return
@@ -135,8 +175,9 @@ def make_loaders(cfg, worker_id: int, total_workers: int, pin: bool = False):
     test = load_dataset(cfg.dataset, False, cfg.test_samples, cfg.num_classes, cfg.image_size,
                         cfg.seed, cfg.data_root)
     s, e = partition_range(worker_id, total_workers, len(train))
-    tl = BatchLoader(train, s, e, cfg.batch_size, train=True, seed=cfg.seed * 1000 + worker_id, pin=pin)
-    vl = BatchLoader(test, 0, len(test), cfg.batch_size, train=False, seed=0, pin=pin)
+    tl = BatchLoader(train, s, e, cfg.batch_size, train=True, seed=cfg.seed * 1000 + worker_id, pin=pin,
+                     prefetch=4 if pin else 0)
+    vl = BatchLoader(test, 0, len(test), cfg.batch_size, train=False, seed=0, pin=pin, prefetch=4 if pin else 0)
     return tl, vl, (s, e)
 
 

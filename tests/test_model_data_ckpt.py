@@ -74,3 +74,22 @@ def test_checkpoint_loads_into_reference_model_strict(ref_modules, tmp_path):
     assert side["global_step"] == 17 and side["shard_versions"] == [17] * 8
     assert set(side["momentum"]) == {n for n, _ in ours.named_parameters()}
     assert len(sd) == 122
+
+
+def test_loader_prefetch_thread_is_transparent():
+    """Background producer (role of the reference's DataLoader worker processes, worker.py:181-187): same batches in
+    the same order, and abandoning the iterator early does not hang."""
+    import torch
+    from dps_b200.utils import data as D
+    ds = D.synthetic_dataset(640, 10, 32, 0)
+    plain = D.BatchLoader(ds, 0, 640, 64, train=True, seed=5)
+    pre = D.BatchLoader(ds, 0, 640, 64, train=True, seed=5, prefetch=3)
+    n = 0
+    for (x1, y1), (x2, y2) in zip(plain, pre):
+        assert torch.equal(x1, x2) and torch.equal(y1, y2)
+        n += 1
+    assert n == 10
+    for i, _ in enumerate(pre):
+        if i == 1:
+            break
+    assert len(list(pre)) == 10
