@@ -335,8 +335,8 @@ class Worker:
                 continue
             n = int(y.numel())
             if n != B:                                   # static shapes: pad the tail batch
-                xp = torch.zeros(B, *x.shape[1:], dtype=x.dtype)
-                yp = torch.full((B,), -1, dtype=y.dtype)
+                xp = torch.zeros(B, *x.shape[1:], dtype=x.dtype, device=x.device)
+                yp = torch.full((B,), -1, dtype=y.dtype, device=y.device)
                 xp[:n], yp[:n] = x, y
                 x, y = xp, yp
             correct += self.engine.eval_batch(x, y)

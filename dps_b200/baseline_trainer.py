@@ -141,7 +141,7 @@ def _train_device(cfg: Config, metrics: TrainingMetrics, milestones, gamma, log,
     from .api import Job
     job = Job(cfg.replace(workers=1, mode="sync", sync_steps=1), rank=0, world=1, device_index=0)
     wk = job.worker
-    train_loader, test_loader, _ = D.make_loaders(cfg, 0, 1, pin=True)
+    train_loader, test_loader, _ = D.make_loaders(cfg, 0, 1, pin=True, device=job.device)
     steps = 0
     try:
         for epoch in range(cfg.epochs):

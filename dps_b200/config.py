@@ -61,6 +61,7 @@ class Config:
     data_root: str = "./data"
     train_samples: int = 50000
     test_samples: int = 10000
+    data_on_device: bool = True           # GPU path: dataset resident in HBM, augmentation kernel per batch
     # ---- device path -------------------------------------------------------
     device: str = "auto"                  # 'auto' | 'cpu' | 'cuda'
     engine: str = "native"                # 'native' (sm_100a kernels) | 'torch' (ATen/cuDNN)
@@ -127,6 +128,8 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--train-samples", type=int, default=50000)
     p.add_argument("--test-samples", type=int, default=10000)
     p.add_argument("--image-size", type=int, default=32)
+    p.add_argument("--data-on-host", dest="data_on_device", action="store_false",
+                   help="GPU path: produce batches on the host (loader thread + pinned H2D) instead of on the device")
     p.add_argument("--device", choices=["auto", "cpu", "cuda"], default="auto")
     p.add_argument("--engine", choices=["native", "torch"], default="native")
     p.add_argument("--bn-buffer-policy", choices=["reference", "local", "mean"], default="mean")

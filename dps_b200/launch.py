@@ -36,7 +36,7 @@ def _worker_main(argv: List[str]) -> int:
     ns = p.parse_args(argv)
     cfg = CFG.from_args(ns)
     job = Job(cfg)
-    train, test, part = D.make_loaders(job.cfg, job.rank, job.world, pin=True)
+    train, test, part = D.make_loaders(job.cfg, job.rank, job.world, pin=True, device=job.device)
     if job.rank == 0:
         print(f"[dps_b200] {job.world} GPU(s), mode={cfg.mode}, batch={cfg.batch_size}/worker, "
               f"partition of rank 0 = {part}", flush=True)

@@ -166,7 +166,7 @@ class BatchLoader:
             yield x, y
 
 
-def make_loaders(cfg, worker_id: int, total_workers: int, pin: bool = False):
+def make_loaders(cfg, worker_id: int, total_workers: int, pin: bool = False, device=None):
     """(train_loader over this worker's partition, test_loader over the full test set).
     Every worker sees the whole test set, as in the reference (worker.py:189-194);
     use ``evaluate(..., shard=(rank, world))`` to split the work."""
@@ -175,6 +175,12 @@ def make_loaders(cfg, worker_id: int, total_workers: int, pin: bool = False):
     test = load_dataset(cfg.dataset, False, cfg.test_samples, cfg.num_classes, cfg.image_size,
                         cfg.seed, cfg.data_root)
     s, e = partition_range(worker_id, total_workers, len(train))
+    if device is not None and getattr(cfg, "data_on_device", True) and torch.device(device).type == "cuda":
+        # B200 path: dataset resident in HBM, one augmentation kernel per batch, no host work per step
+        from .device_data import DeviceLoader
+        tl = DeviceLoader(train, s, e, cfg.batch_size, train=True, seed=cfg.seed * 1000 + worker_id, device=device)
+        vl = DeviceLoader(test, 0, len(test), cfg.batch_size, train=False, seed=0, device=device)
+        return tl, vl, (s, e)
     tl = BatchLoader(train, s, e, cfg.batch_size, train=True, seed=cfg.seed * 1000 + worker_id, pin=pin,
                      prefetch=4 if pin else 0)
     vl = BatchLoader(test, 0, len(test), cfg.batch_size, train=False, seed=0, pin=pin, prefetch=4 if pin else 0)

@@ -70,6 +70,16 @@ int dps_head_forward_backward(const void* act, const void* w, const float* bias,
 /* ---- stem input staging: fp32 NCHW images -> bf16 im2col rows [N*H*W][64] (27 valid columns) ---- */
 int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* stream);
 
+/* ---- device-resident input pipeline (reference: src/workers/worker.py:146-158 transforms, :181-187 DataLoader):
+ *      out[b] = Normalize(ToTensor(Flip(Crop(ZeroPad(src[idx[b]], pad))))) as fp32 NCHW, out_labels[b] = src_labels[idx[b]].
+ *      src is the uint8 NHWC dataset in device memory.  train != 0: crop offsets (dy, dx in [0, 2*pad]) and the flip bit
+ *      come from splitmix64(seed * 0x100000001B3 + counter0 + b): dy = z % (2*pad+1), dx = (z >> 16) % (2*pad+1),
+ *      flip = (z >> 40) & 1.  train == 0: centre crop, no flip.  Rows b >= n_valid are zero-filled with label -1. ---- */
+int dps_augment_batch(const unsigned char* src, const long long* src_labels, const long long* idx, float* out,
+                      long long* out_labels, int B, int S, int n_valid, unsigned long long seed,
+                      unsigned long long counter0, int train, int pad, const float* mean3, const float* std3,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif
