@@ -69,6 +69,10 @@ def main(argv=None) -> int:
     extra = ["--epochs", str(a.epochs), "--batch-size", str(a.batch_size), "--lr", str(a.lr),
              "--train-samples", str(a.train_samples), "--test-samples", str(a.test_samples),
              "--dataset", a.dataset] + [r for r in rest if r != "--"]
+    if a.dataset == "synthetic":                     # generate once here; every rank of every run then loads the cache
+        from .utils import data as D
+        D.load_dataset("synthetic", True, a.train_samples, 100, 32, 0)
+        D.load_dataset("synthetic", False, a.test_samples, 100, 32, 0)
     if not a.no_baseline:
         from . import baseline_trainer as BT
         BT.main(["--epochs", str(a.epochs), "--batch-size", str(a.batch_size), "--lr", str(a.lr),

@@ -12,6 +12,9 @@ from __future__ import annotations
 from dataclasses import dataclass
 from typing import Iterator, Optional, Tuple
 
+import os
+import time
+
 import numpy as np
 import torch
 
@@ -43,7 +46,46 @@ class ArrayDataset:
 def synthetic_dataset(n: int, num_classes: int = 100, image_size: int = 32, seed: int = 0,
                       learnable: bool = True) -> ArrayDataset:
     """Deterministic CIFAR-100-shaped data.  With ``learnable`` each class has a fixed
-    low-frequency template plus noise, so accuracy moves when training works."""
+    low-frequency template plus noise, so accuracy moves when training works.
+
+    Large sets are generated once per machine and cached as .npz (``DPS_DATA_CACHE`` = directory, or ``0`` to
+    disable): with one process per GPU, eight ranks generating the same 150 MB at start-up was the slowest part of a
+    short job.  One rank generates (exclusive lock file), the others wait for the file."""
+    cache = os.environ.get("DPS_DATA_CACHE", os.path.join(
+        os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__)))), "build", "data_cache"))
+    if n < 10000 or cache == "0":
+        return _synthetic_dataset(n, num_classes, image_size, seed, learnable)
+    path = os.path.join(cache, f"synth_n{n}_k{num_classes}_s{image_size}_seed{seed}_{int(learnable)}.npz")
+    lock = path + ".lock"
+    try:
+        os.makedirs(cache, exist_ok=True)
+        deadline = time.time() + 120.0
+        while True:
+            if os.path.exists(path):
+                with np.load(path) as z:
+                    return ArrayDataset(z["images"], z["labels"])
+            try:
+                fd = os.open(lock, os.O_CREAT | os.O_EXCL | os.O_WRONLY)
+            except FileExistsError:
+                if time.time() > deadline:
+                    break                              # the generating rank died: fall through and generate locally
+                time.sleep(0.05)
+                continue
+            try:
+                ds = _synthetic_dataset(n, num_classes, image_size, seed, learnable)
+                tmp = f"{path}.{os.getpid()}.tmp.npz"
+                np.savez(tmp, images=ds.images, labels=ds.labels)
+                os.replace(tmp, path)
+                return ds
+            finally:
+                os.close(fd)
+                os.unlink(lock)
+    except OSError:
+        pass
+    return _synthetic_dataset(n, num_classes, image_size, seed, learnable)
+
+
+def _synthetic_dataset(n: int, num_classes: int, image_size: int, seed: int, learnable: bool) -> ArrayDataset:
     rng = np.random.default_rng(seed)
     labels = rng.integers(0, num_classes, size=n, dtype=np.int64)
     if learnable:
