@@ -353,6 +353,8 @@ class Worker:
     # ------------------------------------------------------------------ loop (reference: worker.py:350-403)
     def run_training(self, train_loader, test_loader=None, epochs: Optional[int] = None,
                      max_steps: Optional[int] = None, eval_batches: Optional[int] = None) -> dict:
+        if self.cfg.use_cuda_graph and self.engine_kind == "native" and self.graph is None:
+            self._build_graph()                             # one-time capture is set-up, not epoch time
         self.training_start_time = time.time()
         epochs = self.cfg.epochs if epochs is None else epochs
         done = False
