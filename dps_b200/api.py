@@ -318,6 +318,63 @@ class Worker:
         self._consumed[k].record(main)
         self._stage_uses += 1
 
+    # ------------------------------------------------------------------ tracing
+    def profile_phases(self, images: torch.Tensor, labels: torch.Tensor, reps: int = 10) -> Dict[str, float]:
+        """Device time per phase of a step in microseconds (CUDA events on the launching stream, eager launches,
+        mean over `reps`, MAX over ranks): input staging, forward (includes the overlapped pull in sync mode),
+        backward, exchange (push + reduce/SGD [+ pull]).  The steps are REAL steps (weights move).  The reference
+        only has wall-clock timers around the optimizer call and the epoch (server.py:121-143, worker.py:355-387).
+        With DPS_NVTX=1 the same phases are NVTX ranges for an external profiler."""
+        nvtx = os.environ.get("DPS_NVTX", "0") == "1"
+        names = ["stage_batch", "forward", "backward", "exchange"]
+        acc = {n: 0.0 for n in names}
+
+        class _R:
+            def __init__(self, name): self.name = name
+            def __enter__(self):
+                if nvtx: torch.cuda.nvtx.range_push("dps/" + self.name)
+            def __exit__(self, *a):
+                if nvtx: torch.cuda.nvtx.range_pop()
+
+        native = self.engine_kind == "native"
+        for rep in range(reps + 1):                       # rep 0 is a warm-up
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(5)]
+            ev[0].record()
+            with _R("stage_batch"):
+                self._stage_batch(images, labels)
+            ev[1].record()
+            with _R("forward"):
+                self._pre()
+                if native:
+                    for f in self.engine.fwd:
+                        f()
+            ev[2].record()
+            with _R("backward"):
+                if native:
+                    for f in self.engine.bwd:
+                        f()
+                else:
+                    self.engine.forward_backward()       # autograd: forward and backward are one call
+            ev[3].record()
+            with _R("exchange"):
+                self._exchange()
+            ev[4].record()
+            if self.cfg.mode == "sync":
+                self.ps.step += 1
+            self.local_step_counter += 1
+            self.images_seen += int(labels.numel())
+            torch.cuda.synchronize(self.job.device)
+            if rep > 0:
+                for i, n in enumerate(names):
+                    acc[n] += ev[i].elapsed_time(ev[i + 1]) * 1e3 / reps
+        t = torch.tensor([acc[n] for n in names], device=self.job.device, dtype=torch.float64)
+        if self.world > 1:
+            import torch.distributed as dist
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        out = {n: round(float(v), 2) for n, v in zip(names, t.tolist())}
+        out["total"] = round(sum(out.values()), 2)
+        return out
+
     # ------------------------------------------------------------------ evaluation
     @torch.no_grad()
     def evaluate(self, loader: Iterable[Tuple[torch.Tensor, torch.Tensor]], max_batches: Optional[int] = None,

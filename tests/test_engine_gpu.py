@@ -159,3 +159,26 @@ def test_experiment_pipeline_one_gpu(tmp_path):
     assert res["worker_metrics_aggregated"]["total_local_steps"] == 8
     assert os.path.exists(os.path.join(out, "charts", "scaling_analysis.png"))
     assert os.path.exists(os.path.join(out, "baseline", "baseline_summary.json"))
+
+
+@pytest.mark.gpu
+def test_profile_phases_reports_device_time_per_phase():
+    """Tracing: per-phase device time of real steps, before and after the CUDA graph exists."""
+    from dps_b200 import Config
+    from dps_b200.api import Job
+    job = Job(Config(workers=1, batch_size=128), rank=0, world=1, device_index=0)
+    try:
+        x = torch.randn(128, 3, 32, 32).pin_memory()
+        y = torch.randint(0, 100, (128,)).pin_memory()
+        ph = job.worker.profile_phases(x, y, reps=3)
+        assert set(ph) == {"stage_batch", "forward", "backward", "exchange", "total"}
+        assert all(v > 0 for v in ph.values()) and ph["backward"] > ph["forward"] * 0.8
+        assert 500 < ph["total"] < 50000                      # microseconds; eager launches, so slower than the graph
+        steps0 = job.worker.local_step_counter
+        l1 = job.worker.train_step(x, y).item()               # graph path still works after eager profiling steps
+        ph2 = job.worker.profile_phases(x, y, reps=2)         # and eager steps still work after capture
+        l2 = job.worker.train_step(x, y).item()
+        assert job.worker.local_step_counter == steps0 + 2 + 3
+        assert l1 == l1 and l2 == l2 and ph2["total"] > 0 and job.ps.error_bits() == 0
+    finally:
+        job.close()
