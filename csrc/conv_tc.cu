@@ -298,6 +298,196 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
   if (tmem_empty != nullptr) asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");   // staging is reused by the next tile
 }
 
+// Register-reduction variant of the epilogue: ONE staging tile instead of two.  The column reductions (BN statistics,
+// or the fused BN-backward sums) ride along in the store loop as per-thread accumulators for the thread's 8 channels,
+// are combined by a butterfly over the lanes that hold the same channels, then per warp in shared memory, then in
+// fixed order across warps.  The fused path accumulates sum(dz*x) and centres / scales it once at the end
+// (sum dz*xhat = rstd * (sum dz*x - mean * sum dz)).  Needs kTileM*kPitch + 8 KiB of staging: used where shared memory
+// is the constraint (halo2conv_kernel keeps 144 KiB of weights resident); measured ~2 us slower per launch than
+// conv_epilogue on the epilogue-bound layer-1 kernel, identical results.
+template <int BLOCK_N, int EPI_WARPS>
+__device__ __forceinline__ void conv_epilogue_rr(const ConvParams& p, int grp, int n0, int h0, int w0, int c_out0,
+                                              uint32_t stage, uint32_t tmem_acc, uint64_t* tmem_full,
+                                              uint32_t full_parity, uint64_t* tmem_empty) {
+  constexpr int T = EPI_WARPS * 32;
+  constexpr int kPitch = ConvSmem<BLOCK_N>::kPitch;
+  constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
+  constexpr int kRowsPerPass = T / kChunks;
+  constexpr int kPasses = kTileM / kRowsPerPass;
+  constexpr int kGroup = kPasses < 4 ? kPasses : 4;
+  constexpr int kColsPerWarp = BLOCK_N / (EPI_WARPS / 4);
+  const int et = threadIdx.x - 64;
+  const int ew = et >> 5, lane = et & 31;
+  const int q = (threadIdx.x >> 5) & 3;                 // TMEM lane quadrant of this warp
+  const int row = q * 32 + lane;                        // tile row == pixel index in the box
+  const int col0 = (ew >> 2) * kColsPerWarp;
+  const uint32_t part_s = stage + kTileM * kPitch;      // [EPI_WARPS][2][BLOCK_N] fp32 per-warp partial sums
+  const int chunk = et % kChunks, row0 = et / kChunks;  // chunk == lane % kChunks (kChunks divides 32)
+  const bool fuse = p.fuse_y != nullptr;
+  const bool stats = p.stats != nullptr;
+  const bool use_addend = p.addend != nullptr && (!p.addend_compact || (p.oph[grp] == 0 && p.opw[grp] == 0));
+  // box dims are powers of two: shifts instead of divisions
+  const int bw_sh = p.bw_sh, bhw_sh = p.bhw_sh, bw_m = (1 << bw_sh) - 1, bhw_m = (1 << bhw_sh) - 1;
+  auto out_off = [&](int rr) -> size_t {
+    const int n = n0 + (rr >> bhw_sh), rem = rr & bhw_m;
+    const int oh = (h0 + (rem >> bw_sh)) * p.os + p.oph[grp], ow = (w0 + (rem & bw_m)) * p.os + p.opw[grp];
+    return (((size_t)n * p.out_H + oh) * p.out_W + ow) * p.out_C + c_out0 + chunk * 8;
+  };
+  auto addend_off = [&](int rr) -> size_t {
+    if (!p.addend_compact) return out_off(rr);
+    const int n = n0 + (rr >> bhw_sh), rem = rr & bhw_m;
+    return (((size_t)n * (p.out_H / p.os) + h0 + (rem >> bw_sh)) * (p.out_W / p.os) + w0 + (rem & bw_m)) * p.out_C +
+           c_out0 + chunk * 8;
+  };
+  // Operands that do not depend on the accumulator (residual-gradient addend, y / x of the fused BN) are fetched
+  // in groups of kGroup rows, all loads of a group in flight at once; the first group is issued BEFORE waiting
+  // for the MMAs so its latency hides under the mainloop.
+  uint4 aa[kGroup], ya[kGroup], xa[kGroup];
+  auto issue = [&](int g) {
+#pragma unroll
+    for (int j = 0; j < kGroup; ++j) {
+      const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+      if (use_addend) aa[j] = ld_nc_v4(p.addend + addend_off(rr));
+      if (fuse) {
+        const size_t off = out_off(rr);
+        ya[j] = ld_nc_v4(p.fuse_y + off);
+        xa[j] = ld_nc_v4(p.fuse_x + off);
+      }
+    }
+  };
+  if (use_addend || fuse) issue(0);
+  // per-thread column accumulators for its 8 channels: (sum, sum of squares) or (sum dz, sum dz*xhat)
+  // (the fused path accumulates sum dz*x and centres / scales it once at the end: sum dz*xhat = rstd*(sum dz*x - mean*sum dz))
+  float acc0[8], acc1[8];
+#pragma unroll
+  for (int i = 0; i < 8; ++i) { acc0[i] = 0.f; acc1[i] = 0.f; }
+  mbar_wait(tmem_full, full_parity);
+  tc_fence_after();
+  if constexpr (kColsPerWarp >= 32) {
+#pragma unroll
+    for (int c = 0; c < kColsPerWarp / 32; ++c) {
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_acc + ((uint32_t)(q * 32) << 16) + col0 + c * 32, r);
+      tmem_ld_wait();
+      const uint32_t dst = stage + row * kPitch + (col0 + c * 32) * 2;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        sts_v4(dst + j * 16,
+               make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
+                          pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]))));
+      }
+    }
+  } else {
+    static_assert(kColsPerWarp == 16 || kColsPerWarp >= 32, "unsupported epilogue split");
+    uint32_t r[16];
+    tmem_ld_32x16(tmem_acc + ((uint32_t)(q * 32) << 16) + col0, r);
+    tmem_ld_wait();
+    const uint32_t dst = stage + row * kPitch + col0 * 2;
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      sts_v4(dst + j * 16,
+             make_uint4(pack_bf16x2(__uint_as_float(r[8 * j + 0]), __uint_as_float(r[8 * j + 1])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 2]), __uint_as_float(r[8 * j + 3])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 4]), __uint_as_float(r[8 * j + 5])),
+                        pack_bf16x2(__uint_as_float(r[8 * j + 6]), __uint_as_float(r[8 * j + 7]))));
+    }
+  }
+  tc_fence_before();
+  if (tmem_empty != nullptr) {             // persistent kernels: the accumulator may be overwritten from here on
+    __syncwarp();
+    if (lane == 0) mbar_arrive(tmem_empty);
+  }
+  asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");      // epilogue warps only
+
+  // One pass over the tile: coalesced 16-byte stores, and the column reductions ride along in registers
+  // (BN statistics for fprop; masked gradient + BN-backward sums for dgrad).
+#pragma unroll 1
+  for (int g = 0; g < kPasses / kGroup; ++g) {
+    if (g > 0) issue(g);
+#pragma unroll
+    for (int j = 0; j < kGroup; ++j) {
+      const int rr = row0 + (g * kGroup + j) * kRowsPerPass;
+      const size_t off = out_off(rr);
+      uint4 v = lds_v4(stage + rr * kPitch + chunk * 16);
+      if (use_addend) {
+        const uint4 a = aa[j];
+        float2 x, y;
+        x = unpack_bf16x2(v.x); y = unpack_bf16x2(a.x); v.x = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.y); y = unpack_bf16x2(a.y); v.y = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.z); y = unpack_bf16x2(a.z); v.z = pack_bf16x2(x.x + y.x, x.y + y.y);
+        x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
+      }
+      if (fuse) {
+        const uint4 yv = ya[j];
+        // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
+        auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
+          const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
+          const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
+          return gg & (lo | hi);
+        };
+        v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
+      }
+      st_v4(p.out + off, v);
+      if (stats || fuse) {
+        const uint32_t vv[4] = {v.x, v.y, v.z, v.w};
+        const uint32_t xx[4] = {xa[j].x, xa[j].y, xa[j].z, xa[j].w};
+#pragma unroll
+        for (int h = 0; h < 4; ++h) {
+          const float2 f = unpack_bf16x2(vv[h]);
+          acc0[2 * h] += f.x; acc0[2 * h + 1] += f.y;
+          if (fuse) {
+            const float2 xv = unpack_bf16x2(xx[h]);
+            acc1[2 * h] += f.x * xv.x;
+            acc1[2 * h + 1] += f.y * xv.y;
+          } else {
+            acc1[2 * h] += f.x * f.x; acc1[2 * h + 1] += f.y * f.y;
+          }
+        }
+      }
+    }
+  }
+  if (stats || fuse) {
+    // lanes l, l + kChunks, ... of a warp hold the same 8 channels (different rows): butterfly over those lanes,
+    // then one partial per warp in shared memory, then a fixed-order sum over the warps -> ONE 64-bit fixed-point
+    // atomic per channel and tile (deterministic).
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+#pragma unroll
+      for (int o = kChunks; o < 32; o <<= 1) {
+        acc0[i] += __shfl_xor_sync(0xffffffffu, acc0[i], o);
+        acc1[i] += __shfl_xor_sync(0xffffffffu, acc1[i], o);
+      }
+    }
+    if (lane < kChunks) {
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        sts_f32(part_s + ((ew * 2 + 0) * BLOCK_N + chunk * 8 + i) * 4, acc0[i]);
+        sts_f32(part_s + ((ew * 2 + 1) * BLOCK_N + chunk * 8 + i) * 4, acc1[i]);
+      }
+    }
+    asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");
+    long long* dst = stats ? p.stats : p.fuse_sums;
+    const float sc0 = stats ? (float)kStatSumScale : (float)kGradSumScale;
+    const float sc1 = stats ? (float)kStatSqScale : (float)kGradSumScale;
+    for (int idx = et; idx < 2 * BLOCK_N; idx += T) {
+      const int which = idx / BLOCK_N, ch = idx % BLOCK_N;
+      float acc = 0.f;
+#pragma unroll
+      for (int w = 0; w < EPI_WARPS; ++w) acc += lds_f32(part_s + ((w * 2 + which) * BLOCK_N + ch) * 4);
+      if (fuse && which) {
+        float sdz = 0.f;
+#pragma unroll
+        for (int w = 0; w < EPI_WARPS; ++w) sdz += lds_f32(part_s + ((w * 2) * BLOCK_N + ch) * 4);
+        acc = (acc - p.fuse_mean[c_out0 + ch] * sdz) * p.fuse_rstd[c_out0 + ch];
+      }
+      red_fixed(dst + which * p.out_C + c_out0 + ch, acc, which ? sc1 : sc0);
+    }
+  }
+  if (tmem_empty != nullptr) asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");   // staging is reused by the next tile
+}
+
 // CL > 1: the CL CTAs of a cluster compute CL adjacent N tiles of the SAME pixel tile, so they need the same
 // activation box.  Each CTA fetches 1/CL of its rows and TMA-multicasts them into all CL CTAs (L2->SM activation
 // traffic / CL); the weight tile stays private.  A stage may be refilled only after ALL CL consumers released it:
@@ -646,6 +836,137 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
       const int acc = i & 1;
       conv_epilogue<64, kHaloEpiWarps>(p, 0, n, h0, w0, 0, smem_u32(staging), tmem_base + acc * 64, &tfull[acc],
                                        (i >> 1) & 1, &tempty[acc]);
+    }
+  }
+
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, 128);
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// halo2conv_kernel: the halo scheme for 3x3 stride-1 convolutions with 128 reduction channels (layer2: 16x16
+// images, 128 -> 128 channels; fprop and dgrad).  The output channels are cut into 64-wide slices (gridDim.y); a CTA
+// serves ONE slice for its whole life and keeps that slice's weights resident: 9 taps x 2 reduction blocks x 8 KiB =
+// 144 KiB.  Per 128-pixel tile it loads two halo tiles (one per 64-channel reduction block, 23 KiB each) into a
+// two-slot ring -- the MMAs of block 1 overlap the load of the next tile's block 0 -- and issues 9 x 2 x 4 MMAs into
+// one of two TMEM accumulators.  L2->SM traffic per 128x128 outputs: 2 x 46 KiB instead of 576 KiB for the tap loop
+// (these convs are bound by the per-SM ingest rate, profiles/conv_bound_analysis.md).
+// Shared memory: 144 KiB weights + 46 KiB ring + 26 KiB staging -> the register-reduction epilogue (one staging tile).
+// ------------------------------------------------------------------------------------------
+constexpr int kH2RB = 2;                                          // reduction blocks (128 channels)
+constexpr int kH2Slots = 2;
+constexpr int kH2WBytes = 9 * kH2RB * 8192;                       // 147456
+constexpr int kH2Staging = kTileM * ConvSmem<64>::kPitch + 8192;  // one output tile + per-warp partials
+constexpr int kH2Smem = 1024 + kH2WBytes + kH2Slots * kHaloSlot + kH2Staging + 256;
+static_assert(kH2Smem <= 227 * 1024, "halo2conv_kernel shared memory");
+
+template <bool B_MN>
+__global__ void __launch_bounds__(kHaloThreads, 1) halo2conv_kernel(const __grid_constant__ CUtensorMap tmA,
+                                                                const __grid_constant__ CUtensorMap tmB,
+                                                                const __grid_constant__ ConvParams p) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~uintptr_t(1023));
+  uint8_t* sW = smem;
+  uint8_t* sA = sW + kH2WBytes;
+  uint8_t* staging = sA + kH2Slots * kHaloSlot;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(staging + kH2Staging);
+  uint64_t* fullA = wfull + 1;
+  uint64_t* emptyA = fullA + kH2Slots;
+  uint64_t* tfull = emptyA + kH2Slots;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  pdl_launch_dependents();
+  const int warp = threadIdx.x >> 5;
+  const int c_out0 = blockIdx.y * 64;                  // this CTA's 64-wide slice of the GEMM N dimension
+  if (warp == 0 && elect_one()) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1) {
+    if (elect_one()) {
+      mbar_init(wfull, 1);
+      for (int s = 0; s < kH2Slots; ++s) { mbar_init(&fullA[s], 1); mbar_init(&emptyA[s], 1); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], kHaloEpiWarps); }
+      fence_barrier_init();
+    }
+    __syncwarp();
+    tmem_alloc(tmem_slot, 128);            // two 64-column accumulators
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();
+
+  const int tiles_per_img = p.tiles_w * p.tiles_h;
+  if (warp == 0) {
+    if (elect_one()) {
+      // resident weights: chunk (tap, cb) = [64 rows][64 cols] bf16, 128-byte swizzled
+      mbar_expect_tx(wfull, kH2WBytes);
+      for (int t = 0; t < 9; ++t)
+        for (int cb = 0; cb < kH2RB; ++cb) {
+          uint8_t* dst = sW + (t * kH2RB + cb) * 8192;
+          if (!B_MN) tma_load_2d(dst, &tmB, wfull, p.taps[0][t].k_off + cb * kKBlock, c_out0);   // rows = co slice, cols = k
+          else       tma_load_2d(dst, &tmB, wfull, p.taps[0][t].k_off + c_out0, cb * kKBlock);   // rows = k (co), cols = ci slice
+        }
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+        const int n = t / tiles_per_img, r = t % tiles_per_img;
+        const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
+        for (int cb = 0; cb < kH2RB; ++cb) {
+          const int j = i * kH2RB + cb;
+          const int s = j % kH2Slots, ph = (j / kH2Slots) & 1;
+          mbar_wait(&emptyA[s], ph ^ 1);
+          mbar_expect_tx(&fullA[s], kHaloBytes);
+          tma_load_5d(sA + s * kHaloSlot, &tmA, &fullA[s], cb * kKBlock, w0 - 1, 0, h0 - 1, n);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    if (elect_one()) {
+      constexpr uint32_t idesc = make_idesc_bf16(kTileM, 64, 0, B_MN ? 1 : 0);
+      mbar_wait(wfull, 0);
+      int i = 0;
+      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+        const int acc = i & 1;
+        mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);          // epilogue has drained this accumulator
+        for (int cb = 0; cb < kH2RB; ++cb) {
+          const int j = i * kH2RB + cb;
+          const int s = j % kH2Slots, ph = (j / kH2Slots) & 1;
+          mbar_wait(&fullA[s], ph);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + s * kHaloSlot);
+#pragma unroll
+          for (int tp = 0; tp < 9; ++tp) {
+            const Tap tap = p.taps[0][tp];
+            const uint32_t a_addr = a_base + ((1 + tap.da) * kHaloRowsW + (1 + tap.db)) * 128;
+            const uint64_t adesc = make_smem_desc(a_addr, 16, kHaloRowsW * 128);
+            const uint32_t b_addr = smem_u32(sW + (tp * kH2RB + cb) * 8192);
+            const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+              umma_bf16(tmem_base + acc * 64, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(B_MN ? k * 128 : k * 2),
+                        idesc, (cb | tp | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&emptyA[s]);
+        }
+        umma_commit(&tfull[acc]);
+      }
+    }
+  } else {
+    int i = 0;
+    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+      const int n = t / tiles_per_img, r = t % tiles_per_img;
+      const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
+      const int acc = i & 1;
+      conv_epilogue_rr<64, kHaloEpiWarps>(p, 0, n, h0, w0, c_out0, smem_u32(staging), tmem_base + acc * 64, &tfull[acc],
+                                          (i >> 1) & 1, &tempty[acc]);
     }
   }
 
@@ -1041,6 +1362,7 @@ struct ConvPlan {
   int block_n;
   bool b_mn;
   bool halo;                      // persistent halo kernel (layer1-type convs)
+  bool halo2;                     // halo2conv_kernel (128 reduction channels, 64-wide resident weight slices)
   int cluster;                    // CTAs per cluster along N (activation multicast); 1 = none
   bool pair;                      // pairconv_kernel (cta_group::2)
   CUtensorMap tmA, tmB;
@@ -1090,6 +1412,18 @@ static int launch_halo(const ConvPlan& pl, cudaStream_t st) {
     configured = true;
   }
   DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kHaloThreads), kHaloSmem, st, pl.tmA, pl.tmB, pl.cp));
+  return 0;
+}
+
+template <bool MN_>
+static int launch_halo2(const ConvPlan& pl, cudaStream_t st) {
+  auto kern = halo2conv_kernel<MN_>;
+  static bool configured = false;
+  if (!configured) {
+    DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, kH2Smem));
+    configured = true;
+  }
+  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kHaloThreads), kH2Smem, st, pl.tmA, pl.tmB, pl.cp));
   return 0;
 }
 
@@ -1180,13 +1514,21 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     pl->halo = !(e && e[0] == '0') && R == 3 && stride == 1 && red == 64 && ngemm == 64 && H % kHaloH == 0 &&
                W % kHaloW == 0;
   }
-  if (pl->halo) {
+  {
+    // 128 reduction channels: resident 64-wide weight slices (DPS_HALO2=1 enables; validated shapes: 16x16 images)
+    const char* e = getenv("DPS_HALO2");
+    pl->halo2 = (e && e[0] == '1') && !pl->halo && R == 3 && stride == 1 && red == 64 * kH2RB && ngemm <= 148 * 64 &&
+                H % kHaloH == 0 && W % kHaloW == 0;
+  }
+  const bool any_halo = pl->halo || pl->halo2;
+  if (any_halo) {
     cp.BW = kHaloW; cp.BH = kHaloH; cp.BN = 1;
   } else if (!pick_box(kTileM, N, TH, TW, &cp.BW, &cp.BH, &cp.BN)) {
     delete pl;
     DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
   }
-  if (pl->halo) { pl->cluster = 1; pl->pair = false; }
+  if (any_halo) { pl->cluster = 1; pl->pair = false; }
+  if (pl->halo2) pl->block_n = 64;
   while (pl->cluster > 1 && (kTileM / pl->cluster) % cp.BW != 0) pl->cluster /= 2;   // a slice is whole box lines
   // each CTA of a cluster loads 128/cluster rows of the box: sub-box = BW x sub_bh x sub_bn
   const int lines = kTileM / pl->cluster / cp.BW;
@@ -1221,7 +1563,7 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         cp.taps[0][nt++] = t;
       }
     cp.ntaps[0] = nt;
-    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (pl->halo ? 2 : 0), sub_bh + (pl->halo ? 2 : 0),
+    rc = make_act_map(&pl->tmA, x, N, H, W, Cin, stride == 2, 64, cp.BW + (any_halo ? 2 : 0), sub_bh + (any_halo ? 2 : 0),
                       sub_bn);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, pl->pair ? 64 : pl->block_n);  // pair: half tile per CTA
   } else {
@@ -1259,7 +1601,7 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
         }
       cp.ngroups = g;
     }
-    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW + (pl->halo ? 2 : 0), sub_bh + (pl->halo ? 2 : 0),
+    rc = make_act_map(&pl->tmA, x, N, Ho, Wo, Cout, 0, 64, cp.BW + (any_halo ? 2 : 0), sub_bh + (any_halo ? 2 : 0),
                       sub_bn);
     if (!rc) rc = make_w_map(&pl->tmB, w, Cout, w_cols, w_pitch, 64, 64);
   }
@@ -1273,6 +1615,11 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   if (pl->halo) {
     cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
     pl->grid = dim3(cp.tiles_total < 148 ? cp.tiles_total : 148, 1, 1);      // persistent: one CTA per SM
+  }
+  if (pl->halo2) {
+    cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
+    const int slices = ngemm / 64, per = 148 / slices;                         // one CTA per SM, `per` CTAs per slice
+    pl->grid = dim3(cp.tiles_total < per ? cp.tiles_total : per, slices, 1);
   }
   *out_plan = pl;
   return 0;
@@ -1400,6 +1747,7 @@ DPS_API int dps_conv_plan_run(void* plan, void* stream) {
   if (pl->kind == 2 && pl->whalo) return launch_wgrad_halo(*pl, st);
   if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
   if (pl->halo) return pl->b_mn ? launch_halo<true>(*pl, st) : launch_halo<false>(*pl, st);
+  if (pl->halo2) return pl->b_mn ? launch_halo2<true>(*pl, st) : launch_halo2<false>(*pl, st);
   if (pl->pair) return pl->b_mn ? launch_pair<true>(*pl, st) : launch_pair<false>(*pl, st);
   if (pl->block_n == 64 && pl->cluster == 4)
     return pl->b_mn ? launch_tapconv<64, true, 4>(*pl, st) : launch_tapconv<64, false, 4>(*pl, st);
@@ -1421,6 +1769,7 @@ DPS_API int dps_conv_plan_info(void* plan, int* grid_xyz, int* block_n, int* sme
   *smem_bytes = (pl->kind == 2 && pl->whalo) ? 1024 + pl->whp.nstages * kWhStage + 256
                 : pl->kind == 2 ? WgradSmem<64>::total(pl->wp.nstages, pl->wp.stage_bytes)
                 : pl->halo   ? kHaloSmem
+                : pl->halo2  ? kH2Smem
                               : (pl->block_n == 128 ? ConvSmem<128>::total(pl->cp.nstages)
                                                     : ConvSmem<64>::total(pl->cp.nstages));
   return 0;

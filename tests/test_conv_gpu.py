@@ -155,3 +155,55 @@ def test_dgrad_with_fused_bn_backward_reduction(shape):
     got = sums.double() / 2 ** 40
     assert torch.allclose(got[:Cin].float(), dzf.sum(0), rtol=2e-3, atol=5e-2)
     assert torch.allclose(got[Cin:].float(), (dzf * xhat).sum(0), rtol=2e-3, atol=5e-2)
+
+
+@pytest.mark.parametrize("Nb", [8, 128])
+def test_halo2_layer2_kernels(monkeypatch, Nb):
+    """halo2conv_kernel (DPS_HALO2=1): 3x3 stride-1, 128 reduction channels, resident 64-wide weight slices, halo tiles,
+    register-reduction epilogue.  fprop + statistics, dgrad + addend, dgrad + fused BN-backward sums."""
+    from dps_b200.ops.conv import ConvPlan
+    monkeypatch.setenv("DPS_HALO2", "1")
+    H, C, R = 16, 128, 3
+    g = torch.Generator(device="cuda").manual_seed(3)
+    x = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.randn(C, R, R, C, device="cuda", generator=g) / (9 * C) ** 0.5).to(torch.bfloat16)
+    dy = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    xf = x.float().permute(0, 3, 1, 2).contiguous().requires_grad_(True)
+    wf = w.float().permute(0, 3, 1, 2).contiguous()
+    y = F.conv2d(xf, wf, padding=1)
+    y.backward(dy.float().permute(0, 3, 1, 2))
+    y_ref, dx_ref = y.detach().permute(0, 2, 3, 1), xf.grad.permute(0, 2, 3, 1)
+    # fprop + BN statistics
+    out = torch.zeros(Nb, H, H, C, device="cuda", dtype=torch.bfloat16)
+    stats = torch.zeros(2 * C, device="cuda", dtype=torch.int64)
+    plan = ConvPlan.fprop(x, w, out, N=Nb, H=H, W=H, Cin=C, Cout=C, R=R, stride=1, stats=stats)
+    assert plan.grid[1] == 2 and plan.grid[0] == min(Nb * 2, 74) and plan.smem > 200 * 1024      # the halo2 path
+    plan.run()
+    torch.cuda.synchronize()
+    assert _relerr(out, y_ref) < 1.5e-2
+    of = out.float().reshape(-1, C)
+    assert torch.allclose((stats[:C].double() / 2 ** 32).float(), of.sum(0), rtol=1e-3, atol=5e-2)
+    assert torch.allclose((stats[C:].double() / 2 ** 24).float(), (of * of).sum(0), rtol=1e-3, atol=5e-1)
+    # dgrad + residual addend
+    res = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    dx = torch.zeros_like(res)
+    plan = ConvPlan.dgrad(dy, w, dx, N=Nb, H=H, W=H, Cin=C, Cout=C, R=R, stride=1, addend=res)
+    assert plan.grid[1] == 2
+    plan.run()
+    torch.cuda.synchronize()
+    assert _relerr(dx, dx_ref + res.float()) < 2e-2
+    # dgrad + fused BN-backward reduction
+    ybn = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    xbn = torch.randn(Nb, H, H, C, device="cuda", generator=g).to(torch.bfloat16)
+    mean = torch.randn(C, device="cuda", generator=g) * 0.1
+    rstd = torch.rand(C, device="cuda", generator=g) + 0.5
+    sums = torch.zeros(2 * C, device="cuda", dtype=torch.int64)
+    dz = torch.empty(Nb, H, H, C, device="cuda", dtype=torch.bfloat16)
+    ConvPlan.dgrad(dy, w, dz, N=Nb, H=H, W=H, Cin=C, Cout=C, R=R, stride=1).fuse_bn_bwd(ybn, xbn, mean, rstd, sums).run()
+    torch.cuda.synchronize()
+    assert _relerr(dz, dx_ref * (ybn.float() > 0)) < 2e-2
+    dzf = dz.float().reshape(-1, C)
+    xhat = (xbn.float().reshape(-1, C) - mean) * rstd
+    got = sums.double() / 2 ** 40
+    assert torch.allclose(got[:C].float(), dzf.sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
+    assert torch.allclose(got[C:].float(), (dzf * xhat).sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
