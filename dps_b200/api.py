@@ -275,15 +275,26 @@ class Worker:
         else:
             self._pre()
             self.engine.forward_backward()
-        self._accum += 1
-        if self._accum >= self.cfg.sync_steps:
-            if not fused_exchange:
-                if self._accum > 1:
-                    self.ps.grad[self.rank].div_(self._accum)       # Q12: accumulate, not discard
+        if self.cfg.sync_steps > 1 and self.cfg.local_step_policy == "reference":
+            # reference behaviour (worker.py:367-377): fetch + push only on the first batch of every k; the other
+            # k-1 batches still run forward/backward but their gradients are thrown away
+            if self._accum == 0:
                 self._exchange()
-            if self.cfg.mode == "sync":
-                self.ps.step += 1
-            self._accum = 0
+                if self.cfg.mode == "sync":
+                    self.ps.step += 1
+            else:
+                self.ps.grad[self.rank].zero_()
+            self._accum = (self._accum + 1) % self.cfg.sync_steps
+        else:
+            self._accum += 1
+            if self._accum >= self.cfg.sync_steps:
+                if not fused_exchange:
+                    if self._accum > 1:
+                        self.ps.grad[self.rank].div_(self._accum)       # Q12: accumulate, not discard
+                    self._exchange()
+                if self.cfg.mode == "sync":
+                    self.ps.step += 1
+                self._accum = 0
         slot = self.local_step_counter % len(self._ring)
         self._ring[slot].copy_(self.engine.out, non_blocking=True)
         self._events[slot].record()

@@ -182,3 +182,35 @@ def test_profile_phases_reports_device_time_per_phase():
         assert l1 == l1 and l2 == l2 and ph2["total"] > 0 and job.ps.error_bits() == 0
     finally:
         job.close()
+
+
+@pytest.mark.gpu
+def test_sync_steps_reference_policy_discards_and_accumulate_policy_averages():
+    """--sync-steps k.  'reference': only the first batch of every k is pushed, the other k-1
+    gradients are thrown away (worker.py:367-377).  'accumulate' (default): the mean of the k gradients is pushed."""
+    from dps_b200 import Config
+    from dps_b200.api import Job
+    g = torch.Generator().manual_seed(0)
+    xs = [torch.randn(32, 3, 32, 32, generator=g) for _ in range(3)]
+    ys = [torch.randint(0, 100, (32,), generator=g) for _ in range(3)]
+
+    def run(steps, policy, batches):
+        cfg = Config(mode="sync", workers=1, batch_size=32, lr=0.05, sync_steps=steps, local_step_policy=policy, seed=3)
+        job = Job(cfg, rank=0, world=1, device_index=0)
+        try:
+            for i in batches:
+                job.worker.train_step(xs[i], ys[i]).item()
+            torch.cuda.synchronize()
+            return job.server.global_step, {k: v.clone() for k, v in job.server.state_dict().items()
+                                            if v.dtype.is_floating_point and "running" not in k}
+        finally:
+            job.close()
+
+    step_one, w_one = run(1, "accumulate", [0])                  # one plain step on batch 0
+    step_ref, w_ref = run(3, "reference", [0, 1, 2])             # k = 3, reference policy: only batch 0 counts
+    assert step_one == step_ref == 1
+    for k in w_one:
+        assert torch.allclose(w_one[k], w_ref[k], rtol=1e-4, atol=1e-5), k
+    step_acc, w_acc = run(3, "accumulate", [0, 1, 2])            # k = 3, accumulate: a different (averaged) update
+    assert step_acc == 1
+    assert any(not torch.allclose(w_one[k], w_acc[k], rtol=1e-4, atol=1e-5) for k in w_one)
