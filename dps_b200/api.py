@@ -255,24 +255,36 @@ class Worker:
     def _build_graph(self) -> None:
         self.ps.use_device_counters(True)
         saved = {k: v.clone() for k, v in self.engine.bn_buffers().items()}   # warm-up must not count as a step
-        self.engine.capture(extra=self._exchange if self.cfg.sync_steps == 1 else None, pre=self._pre)
+        self._ensure_staging()
+        fused = self.cfg.sync_steps == 1
+        # one graph per staging slot: graph k reads the batch straight from slot k and ends with the D2H copy of
+        # (loss, #correct) into pinned slot k -- no eager copies between two replays
+        self.engine.capture(extra=self._exchange if fused else None, pre=self._pre,
+                            inputs=list(zip(self._stage_x, self._stage_y)),
+                            post=lambda k: self._ring[k].copy_(self.engine.out, non_blocking=True))
         for k, v in self.engine.bn_buffers().items():
             v.copy_(saved[k])
         # capture ran one eager warm-up step on the engine only: clear what it accumulated
         self.ps.grad[self.rank].zero_()
         self.graph = self.engine.graph
+        self.graphs = self.engine.graphs
         torch.cuda.synchronize(self.job.device)
 
     def train_step(self, images: torch.Tensor, labels: torch.Tensor) -> LossHandle:
-        """One local batch.  `images` fp32 [B,3,S,S] and `labels` int64 [B] (host, ideally pinned)."""
+        """One local batch.  `images` fp32 [B,3,S,S] and `labels` int64 [B]: pinned host tensors (copied on a side
+        stream, overlapping the previous step), device tensors, or pageable host tensors.  The returned handle is
+        valid until two further steps have been issued (its pinned slot is then reused)."""
         use_graph = self.cfg.use_cuda_graph and self.engine_kind == "native"
         if use_graph and self.graph is None:
             self._build_graph()
-        self._stage_batch(images, labels)
         fused_exchange = use_graph and self.cfg.sync_steps == 1
         if use_graph:
-            self.graph.replay()
+            k = self._stage_batch(images, labels, handover=False)
+            self.graphs[k].replay()
+            self._consumed[k].record()
         else:
+            k = None
+            self._stage_batch(images, labels)
             self._pre()
             self.engine.forward_backward()
         if self.cfg.sync_steps > 1 and self.cfg.local_step_policy == "reference":
@@ -295,39 +307,54 @@ class Worker:
                 if self.cfg.mode == "sync":
                     self.ps.step += 1
                 self._accum = 0
-        slot = self.local_step_counter % len(self._ring)
-        self._ring[slot].copy_(self.engine.out, non_blocking=True)
+        if k is None:                                    # eager path: read the result back with an eager copy
+            slot = 2 + self.local_step_counter % 2       # slots 0, 1 belong to the graphs
+            self._ring[slot].copy_(self.engine.out, non_blocking=True)
+        else:
+            slot = k
         self._events[slot].record()
         self.local_step_counter += 1
         self.images_seen += int(labels.numel())
         return LossHandle(self._ring[slot], self._events[slot])
 
-    def _stage_batch(self, images: torch.Tensor, labels: torch.Tensor) -> None:
-        """H2D of the batch on a side stream into one of two staging buffers (overlaps the previous step's
-        kernels), then a device-to-device hand-over into the engine's static input on the compute stream."""
-        if not (images.is_pinned() and labels.is_pinned()) or not hasattr(self.engine, "images"):
-            self.engine.load_batch(images, labels)
+    def _ensure_staging(self) -> None:
+        if hasattr(self, "_copy_stream"):
             return
-        if not hasattr(self, "_copy_stream"):
-            self._copy_stream = torch.cuda.Stream(device=self.job.device)
-            self._stage_x = [torch.empty_like(self.engine.images) for _ in range(2)]
-            self._stage_y = [torch.empty_like(self.engine.labels) for _ in range(2)]
-            self._h2d_done = [torch.cuda.Event() for _ in range(2)]
-            self._consumed = [torch.cuda.Event() for _ in range(2)]
-            self._stage_uses = 0
+        self._copy_stream = torch.cuda.Stream(device=self.job.device)
+        self._stage_x = [torch.zeros_like(self.engine.images) for _ in range(2)]
+        self._stage_y = [torch.zeros_like(self.engine.labels) for _ in range(2)]
+        self._h2d_done = [torch.cuda.Event() for _ in range(2)]
+        self._consumed = [torch.cuda.Event() for _ in range(2)]
+        self._stage_uses = 0
+
+    def _stage_batch(self, images: torch.Tensor, labels: torch.Tensor, handover: bool = True) -> int:
+        """Bring the batch into staging slot k = (#batches staged) % 2 and return k.  Pinned host batches are copied
+        on a side stream (overlaps the previous step's kernels; the slot is reused only after the step that read it
+        two batches ago has finished); anything else is copied on the compute stream.  handover=True also copies the
+        slot into the engine's own input buffers (eager launches read those; graph k reads slot k directly)."""
+        if not hasattr(self.engine, "images"):
+            self.engine.load_batch(images, labels)
+            return 0
+        self._ensure_staging()
         k = self._stage_uses % 2
         main = torch.cuda.current_stream()
-        with torch.cuda.stream(self._copy_stream):
-            if self._stage_uses >= 2:
-                self._copy_stream.wait_event(self._consumed[k])     # staging slot k was handed over two steps ago
+        if images.is_pinned() and labels.is_pinned():
+            with torch.cuda.stream(self._copy_stream):
+                if self._stage_uses >= 2:
+                    self._copy_stream.wait_event(self._consumed[k])
+                self._stage_x[k].copy_(images, non_blocking=True)
+                self._stage_y[k].copy_(labels, non_blocking=True)
+                self._h2d_done[k].record(self._copy_stream)
+            main.wait_event(self._h2d_done[k])
+        else:
             self._stage_x[k].copy_(images, non_blocking=True)
             self._stage_y[k].copy_(labels, non_blocking=True)
-            self._h2d_done[k].record(self._copy_stream)
-        main.wait_event(self._h2d_done[k])
-        self.engine.images.copy_(self._stage_x[k], non_blocking=True)
-        self.engine.labels.copy_(self._stage_y[k], non_blocking=True)
-        self._consumed[k].record(main)
+        if handover:
+            self.engine.images.copy_(self._stage_x[k], non_blocking=True)
+            self.engine.labels.copy_(self._stage_y[k], non_blocking=True)
+            self._consumed[k].record(main)
         self._stage_uses += 1
+        return k
 
     # ------------------------------------------------------------------ tracing (SURVEY §5.1)
     def profile_phases(self, images: torch.Tensor, labels: torch.Tensor, reps: int = 10) -> Dict[str, float]:

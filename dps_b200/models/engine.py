@@ -333,8 +333,13 @@ class ResNetEngine:
             f()
 
     def capture(self, extra: Optional[Callable[[], None]] = None, warmup: int = 1,
-                pre: Optional[Callable[[], None]] = None) -> None:
-        """Capture [pre] + forward + backward + [extra] (e.g. pull fork / push + join) into one CUDA graph."""
+                pre: Optional[Callable[[], None]] = None, inputs=None,
+                post: Optional[Callable[[int], None]] = None) -> None:
+        """Capture [pre] + forward + backward + [extra] (e.g. pull fork / push + join) into a CUDA graph.
+
+        `inputs` = [(images, labels), ...]: capture ONE GRAPH PER INPUT BUFFER PAIR (`self.graphs[k]` reads pair k;
+        `post(k)` is captured at the end of graph k, e.g. the D2H copy of the loss).  Replaying graph k while the next
+        batch is copied into pair k^1 removes the device-to-device hand-over of the batch from the step."""
         s = torch.cuda.Stream(device=self.dev)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
@@ -344,16 +349,24 @@ class ResNetEngine:
             self.seg_wait = saved
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
-        g = torch.cuda.CUDAGraph()
-        # 'relaxed': other threads (the loader's pinned-memory allocations) may call the runtime while this thread
-        # captures; nothing inside the capture allocates.
-        with torch.cuda.graph(g, capture_error_mode="relaxed"):
-            if pre is not None:
-                pre()
-            self.forward_backward()
-            if extra is not None:
-                extra()
-        self.graph = g
+        own = (self.images, self.labels)
+        self.graphs = []
+        for k, (x, y) in enumerate(inputs if inputs else [own]):
+            self.images, self.labels = x, y                  # the schedule reads these attributes when it launches
+            g = torch.cuda.CUDAGraph()
+            # 'relaxed': other threads (the loader's pinned-memory allocations) may call the runtime while this
+            # thread captures; nothing inside the capture allocates.
+            with torch.cuda.graph(g, capture_error_mode="relaxed"):
+                if pre is not None:
+                    pre()
+                self.forward_backward()
+                if extra is not None:
+                    extra()
+                if post is not None:
+                    post(k)
+            self.graphs.append(g)
+        self.images, self.labels = own                       # eager / evaluation paths keep the engine's own buffers
+        self.graph = self.graphs[0]
 
     @torch.no_grad()
     def eval_batch(self, images: torch.Tensor, labels: torch.Tensor) -> int:
