@@ -16,6 +16,7 @@ from __future__ import annotations
 
 import threading
 import time
+import warnings
 from typing import Dict, Optional
 
 import grpc
@@ -28,6 +29,11 @@ from ..models.resnet import build_model
 from ..utils import data as D
 from ..utils import metrics as M
 from . import codec, proto
+
+
+_TORCH_DTYPES = {"float32": torch.float32, "float16": torch.float16, "float64": torch.float64,
+                 "int64": torch.int64, "int32": torch.int32, "uint8": torch.uint8, "int8": torch.int8,
+                 "bool": torch.bool, "int16": torch.int16}
 
 
 class DistributedWorker:
@@ -99,6 +105,9 @@ class DistributedWorker:
     # ------------------------------------------------------------------ setup
     def setup_model(self) -> None:
         self.model = build_model(self.cfg.num_classes, seed=self.cfg.seed).to(self.device)
+        self.amp = self.cfg.amp == "bf16"
+        if self.amp:                                  # oneDNN / cuDNN bf16 kernels want NHWC
+            self.model = self.model.to(memory_format=torch.channels_last)
         self.criterion = nn.CrossEntropyLoss()
 
     def setup_data(self) -> None:
@@ -115,14 +124,21 @@ class DistributedWorker:
             self.global_step_cache = rep.global_step
             sd = self.model.state_dict()
             keep_local_bn = self.cfg.bn_buffer_policy == "local" and self.local_step_counter > 0
-            with torch.no_grad():
+            with torch.no_grad(), warnings.catch_warnings():
+                warnings.simplefilter("ignore")       # frombuffer on a read-only frame: we only read from it
                 for name, arr in arrays.items():
                     dst = sd.get(name)
                     if dst is None:
                         continue
                     if keep_local_bn and ("running_" in name or "num_batches" in name):
                         continue
-                    dst.copy_(torch.from_numpy(np.array(arr, copy=True)).to(dst.dtype))
+                    if arr.size == 0:
+                        continue
+                    # zero-copy view of the received frame (read-only is fine: it is only a copy source)
+                    src = torch.frombuffer(arr, dtype=_TORCH_DTYPES[arr.dtype.name]).view(dst.shape) \
+                        if arr.dtype.name in _TORCH_DTYPES and arr.flags.c_contiguous \
+                        else torch.from_numpy(np.array(arr, copy=True))
+                    dst.copy_(src)
         return rep.global_step
 
     def compress_gradients(self, grads: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
@@ -152,7 +168,11 @@ class DistributedWorker:
             if zero:
                 self.model.zero_grad(set_to_none=True)
             data, targets = data.to(self.device), targets.to(self.device)
-            loss = self.criterion(self.model(data), targets)
+            if self.amp:
+                data = data.contiguous(memory_format=torch.channels_last)
+            with torch.autocast(self.device.type, dtype=torch.bfloat16, enabled=self.amp):
+                logits = self.model(data)
+            loss = self.criterion(logits.float(), targets)
             loss.backward()
             self.local_step_counter += 1
             self.images_seen += int(targets.numel())

@@ -89,3 +89,21 @@ def test_sync_step_equals_large_batch_sgd():
         if n in grads_sum:
             expect = p.numpy() - 0.1 * (grads_sum[n] / W)
             np.testing.assert_allclose(sv.parameters[n], expect, rtol=1e-6, atol=1e-7)
+
+
+def test_bf16_autocast_worker_keeps_fp32_master(tmp_path):
+    """--amp bf16 (gRPC/CPU worker): the local step runs under bf16 autocast + channels_last, gradients and the
+    server's master weights stay fp32, and the update is close to the fp32 worker's."""
+    torch.set_num_threads(2)
+    base = Config(mode="sync", workers=1, lr=0.05, batch_size=8, epochs=1, train_samples=16, test_samples=8,
+                  barrier_timeout_s=120, seed=1)
+    sv32, w32 = _run_job(base, steps=1, tmp_path=tmp_path)
+    sv16, w16 = _run_job(base.replace(amp="bf16"), steps=1, tmp_path=tmp_path)
+    assert w16[0].amp and not w32[0].amp
+    a, b = sv32.state_dict_numpy(), sv16.state_dict_numpy()
+    assert all(v.dtype in (np.float32, np.int64) for v in b.values())
+    init = build_model(100, seed=1).state_dict()["fc.weight"].numpy()
+    d32, d16 = a["fc.weight"] - init, b["fc.weight"] - init
+    assert np.abs(d32).max() > 0 and np.abs(d16).max() > 0
+    cos = float((d32 * d16).sum() / (np.linalg.norm(d32) * np.linalg.norm(d16)))
+    assert cos > 0.98, cos
