@@ -100,8 +100,9 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
       for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
         const long long g = global_index(l, o, W, BS);
         F8 v = load_f32x8(grad + g);
-        if (!compress_fp16) {                                 // fp32 wire: two fp16 planes is not lossless; keep
-          // uncompressed mode stores fp32 into a staging buffer twice as large (slot stride 2E halfs)
+        if (!compress_fp16) {
+          // uncompressed wire (compress = 'none'): fp32 straight into the staging slot, which is allocated twice as
+          // large for this mode (slot stride 2E halfs == E floats)
           store_f32x8(reinterpret_cast<float*>(T.stage[o]) + (long long)r * E + l, v);
         } else {
           st_v4(dst + l, to_f16x8(v));
