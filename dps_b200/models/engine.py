@@ -11,7 +11,7 @@ gradient arena, both laid out by ``store/shardmap.py`` -- exactly what the Push/
 from __future__ import annotations
 
 import ctypes as C
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Tuple
 
 import torch

@@ -16,7 +16,7 @@ reject above the bound, weight ``max(0.1, 1/(1+0.1 s))`` in async mode.
 from __future__ import annotations
 
 import ctypes as C
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 

@@ -20,7 +20,6 @@ with the defects listed in SURVEY §2.6 fixed behind flags:
 """
 from __future__ import annotations
 
-import json
 import threading
 import time
 from collections import deque

@@ -21,8 +21,8 @@ BN running statistics (60 buffers) are worker-local state and are not part of th
 """
 from __future__ import annotations
 
-from dataclasses import dataclass, field
-from typing import Dict, List, Mapping, Optional, Tuple
+from dataclasses import dataclass
+from typing import Dict, List, Mapping, Tuple
 
 import torch
 

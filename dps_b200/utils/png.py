@@ -6,7 +6,7 @@ from __future__ import annotations
 
 import struct
 import zlib
-from typing import Sequence, Tuple
+from typing import Tuple
 
 import numpy as np
 

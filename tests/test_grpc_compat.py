@@ -8,7 +8,6 @@ from concurrent import futures
 
 import grpc
 import numpy as np
-import pytest
 
 from dps_b200.config import Config
 from dps_b200.rpc import codec, proto, servicer as S

@@ -1,5 +1,4 @@
 """W13/W14/W16: model parity with the reference module, partitioning, checkpoint compatibility."""
-import numpy as np
 import pytest
 import torch
 

@@ -4,7 +4,6 @@ hammer the handlers in-process and closed-form invariants are checked afterwards
 import threading
 
 import numpy as np
-import pytest
 
 from dps_b200 import Config
 from dps_b200.rpc import codec, proto
