@@ -41,7 +41,7 @@ def _wait_port(port: int, timeout: float = 60.0) -> bool:
 
 
 def run_ours(workers: int, steps: int, batch: int, mode: str, compat_pickle: bool, outdir: str,
-             amp: str = "none") -> dict:
+             amp: str = "none", pull_compress: str = "none") -> dict:
     N, K, B = workers, steps, batch
     train_samples = N * B * K
     port = _free_port()
@@ -56,7 +56,7 @@ def run_ours(workers: int, steps: int, batch: int, mode: str, compat_pickle: boo
         if f.endswith(".json"):
             os.unlink(os.path.join(outdir, f))
     common = ["--train-samples", str(train_samples), "--test-samples", str(B), "--device", "cpu",
-              "--metrics-dir", outdir] + (["--compat-pickle"] if compat_pickle else [])
+              "--metrics-dir", outdir, "--pull-compress", pull_compress] + (["--compat-pickle"] if compat_pickle else [])
     srv = subprocess.Popen([sys.executable, "-m", "dps_b200.rpc.servicer", "--mode", mode, "--workers", str(N),
                             "--port", str(port), "--lr", "0.1"] + common, env=env, cwd=ROOT,
                            stdout=open(os.path.join(outdir, "server.log"), "w"), stderr=subprocess.STDOUT)
@@ -100,7 +100,7 @@ def run_ours(workers: int, steps: int, batch: int, mode: str, compat_pickle: boo
         "data": "synthetic",
         "config": {"model": "ResNet-18 (CIFAR-100 shape, 32x32, random init)", "global_batch": N * B,
                    "transport": "gRPC localhost, " + ("reference pickle payloads" if compat_pickle else "DPS1 frames")
-                                + ", fp16 gradient compression", "device": "CPU", "mode": mode,
+                                + ", fp16 gradient compression, pull " + pull_compress, "device": "CPU", "mode": mode,
                    "timing": "worker epoch wall clock, max over workers, warm-up epoch discarded",
                    "omp_threads_per_worker": int(env["OMP_NUM_THREADS"])},
         "phase_mean_seconds": {k: round(sum(v) / len(v), 4) for k, v in phases.items()},
@@ -117,9 +117,10 @@ def main(argv=None) -> int:
     p.add_argument("--compat-pickle", action="store_true")
     p.add_argument("--with-reference", action="store_true")
     p.add_argument("--amp", choices=["none", "bf16"], default="none")
+    p.add_argument("--pull-compress", choices=["none", "fp16"], default="none")
     p.add_argument("--out", default=os.path.join(ROOT, "gpurun_out", "grpc_cpu_bench"))
     a = p.parse_args(argv)
-    ours = run_ours(a.workers, a.steps, a.batch, a.mode, a.compat_pickle, a.out, a.amp)
+    ours = run_ours(a.workers, a.steps, a.batch, a.mode, a.compat_pickle, a.out, a.amp, a.pull_compress)
     print(json.dumps(ours))
     if a.with_reference:
         from bench_tools.reference_arm import run_reference

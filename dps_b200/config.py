@@ -56,6 +56,7 @@ class Config:
     bn_buffer_policy: str = "mean"        # 'reference' | 'local' | 'mean'   (Q5)
     compat_pickle: bool = False           # accept/emit reference pickle payloads (Q15)
     compress: str = "fp16"                # gradient wire format: 'fp16' | 'none'
+    pull_compress: str = "none"           # gRPC path, FetchParameters payload: 'none' (fp32, reference) | 'fp16'
     amp: str = "none"                     # gRPC/CPU worker compute: 'none' (fp32, reference-exact) | 'bf16' (autocast)
     # ---- data --------------------------------------------------------------
     dataset: str = "synthetic"            # 'synthetic' | 'cifar100'
@@ -86,6 +87,8 @@ class Config:
             raise ValueError("local_step_policy must be reference|accumulate")
         if self.compress not in ("fp16", "none"):
             raise ValueError("compress must be fp16|none")
+        if self.pull_compress not in ("none", "fp16"):
+            raise ValueError("pull_compress must be none|fp16")
         if self.amp not in ("none", "bf16"):
             raise ValueError("amp must be none|bf16")
         if self.sync_steps < 1:
@@ -141,6 +144,8 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--barrier-timeout-s", type=float, default=60.0)
     p.add_argument("--compat-pickle", action="store_true")
     p.add_argument("--compress", choices=["fp16", "none"], default="fp16")
+    p.add_argument("--pull-compress", choices=["none", "fp16"], default="none",
+                   help="gRPC server: send parameters as fp16 (master stays fp32); halves the pull payload")
     p.add_argument("--amp", choices=["none", "bf16"], default="none",
                    help="gRPC/CPU worker: bf16 autocast + channels_last for the local step (master weights stay fp32)")
     p.add_argument("--metrics-dir", default=None)

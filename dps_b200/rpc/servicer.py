@@ -209,7 +209,12 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         with self.param_lock:
             cached = self._fetch_cache.get(as_pickle)
             if cached is None or cached[0] != self.global_step:
-                payload = codec.encode_any(self.parameters, as_pickle, {"global_step": self.global_step})
+                params = self.parameters
+                if self.cfg.pull_compress == "fp16" and not as_pickle:
+                    # floating tensors travel as fp16 (the frame is self-describing; the worker casts back);
+                    # integer buffers (num_batches_tracked) and the fp32 master here are untouched
+                    params = {k: (v.astype(np.float16) if v.dtype == np.float32 else v) for k, v in params.items()}
+                payload = codec.encode_any(params, as_pickle, {"global_step": self.global_step})
                 cached = (self.global_step, payload)
                 self._fetch_cache[as_pickle] = cached
             step, payload = cached

@@ -107,3 +107,30 @@ def test_bf16_autocast_worker_keeps_fp32_master(tmp_path):
     assert np.abs(d32).max() > 0 and np.abs(d16).max() > 0
     cos = float((d32 * d16).sum() / (np.linalg.norm(d32) * np.linalg.norm(d16)))
     assert cos > 0.98, cos
+
+
+def test_pull_compress_fp16_halves_payload_and_keeps_fp32_master(tmp_path):
+    from dps_b200.rpc import codec, proto
+    cfg = Config(mode="sync", workers=1, pull_compress="fp16")
+    sv = S.ParameterServerServicer("sync", 1, 0.1, config=cfg)
+    rep = sv.FetchParameters(proto.FetchRequest(worker_id=0), None)
+    full = S.ParameterServerServicer("sync", 1, 0.1, config=Config(workers=1)).FetchParameters(
+        proto.FetchRequest(worker_id=0), None)
+    assert len(rep.parameters) < 0.51 * len(full.parameters)
+    arrs, _ = codec.decode_any(rep.parameters, allow_pickle=False)
+    assert arrs["conv1.weight"].dtype == np.float16 and arrs["bn1.num_batches_tracked"].dtype == np.int64
+    assert sv.parameters["conv1.weight"].dtype == np.float32
+    assert np.allclose(arrs["conv1.weight"].astype(np.float32), sv.parameters["conv1.weight"], atol=1e-3)
+    # a worker loads the fp16 frame into its fp32 model
+    w = DistributedWorker("unused:0", "w", config=cfg)
+    w.setup_model()
+    w.worker_id = 0
+
+    class _Stub:
+        def FetchParameters(self, req):
+            return rep
+    w.stub = _Stub()
+    w.fetch_parameters()
+    got = w.model.state_dict()["conv1.weight"]
+    assert got.dtype == torch.float32
+    assert torch.allclose(got, torch.from_numpy(sv.parameters["conv1.weight"]), atol=1e-3)
