@@ -44,6 +44,12 @@ class Job:
         self.world = _env_int("WORLD_SIZE", 1) if world is None else world
         self.device_index = _env_int("LOCAL_RANK", self.rank) if device_index is None else device_index
         self.cfg = cfg.replace(workers=self.world).validate()
+        if not torch.cuda.is_available():
+            raise RuntimeError(
+                "dps_b200.api.Job is the on-box device path (one process per B200, NVLink peer memory) and needs CUDA. "
+                "On a machine without a GPU use the gRPC roles: `python -m dps_b200.rpc.servicer` + "
+                "`python -m dps_b200.rpc.client` (or dps_b200.rpc.servicer.build_server / "
+                "dps_b200.rpc.client.DistributedWorker), see INTEGRATION.md.")
         torch.cuda.set_device(self.device_index)
         self.device = torch.device("cuda", self.device_index)
         self.group = None

@@ -50,3 +50,14 @@ def test_proto_contract_script_in_sync():
     r = subprocess.run([sys.executable, os.path.join(root, "scripts", "check_proto.py")], capture_output=True, text=True)
     assert r.returncode == 0, r.stdout + r.stderr
     assert "8 messages, 4 rpcs, OK" in r.stdout
+
+
+def test_job_without_cuda_points_to_the_grpc_path():
+    import pytest
+    import torch
+    from dps_b200 import Config
+    from dps_b200.api import Job
+    if torch.cuda.is_available():
+        pytest.skip("CUDA present")
+    with pytest.raises(RuntimeError, match="gRPC roles"):
+        Job(Config(workers=1), rank=0, world=1, device_index=0)
