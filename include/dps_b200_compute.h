@@ -80,6 +80,13 @@ int dps_augment_batch(const unsigned char* src, const long long* src_labels, con
                       unsigned long long counter0, int train, int pad, const float* mean3, const float* std3,
                       void* stream);
 
+/* ---- hardware probe (no counterpart in the reference; used by bench_tools/exp_halo.py, not by the framework):
+ *      one 128-pixel x 64-channel 3x3 output tile computed from ONE halo tile with shifted-window UMMA descriptors.
+ *      variant selects the descriptor form under test (K-major / MN-major windows, base_offset handling); out is
+ *      [128][64] fp32.  It established that the 128-byte swizzle depends on absolute shared-memory address bits. ---- */
+int dps_exp_halo_tile(const void* x, const void* w, float* out, int N, int H, int W, int n, int h0, int w0, int variant,
+                      void* stream);
+
 #ifdef __cplusplus
 }
 #endif
