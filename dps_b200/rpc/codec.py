@@ -138,13 +138,49 @@ def encode_any(tensors: Mapping[str, np.ndarray], as_pickle: bool, meta: Optiona
     return reference_pickle_dumps(tensors) if as_pickle else encode_frame(tensors, meta)
 
 
+def _torch_cast(a: np.ndarray, np_dtype, torch_dtype) -> np.ndarray:
+    """dtype conversion through torch's vectorised kernels into a fresh numpy array (numpy's own fp32<->fp16
+    casts are scalar code: 10 ms per 2 M elements against 1.3 ms)."""
+    import warnings
+
+    import torch
+    a = np.ascontiguousarray(a)
+    if a.size < 32768:                                # small tensors: the fixed cost of the torch path dominates
+        return a.astype(np_dtype)
+    out = np.empty(a.shape, dtype=np_dtype)
+    if a.size:
+        with warnings.catch_warnings():
+            warnings.simplefilter("ignore")           # read-only source (a received frame): it is only read
+            torch.from_numpy(out).copy_(torch.from_numpy(a) if a.flags.writeable
+                                        else torch.frombuffer(a, dtype=_NP2TORCH[a.dtype.name]).view(a.shape))
+    return out
+
+
+_NP2TORCH: Dict[str, "object"] = {}
+
+
+def _init_torch_map() -> None:
+    if not _NP2TORCH:
+        import torch
+        _NP2TORCH.update({"float16": torch.float16, "float32": torch.float32, "float64": torch.float64,
+                          "int64": torch.int64, "int32": torch.int32, "uint8": torch.uint8, "int8": torch.int8,
+                          "bool": torch.bool, "int16": torch.int16})
+
+
 def compress_gradients(grads: Mapping[str, np.ndarray], how: str = "fp16") -> Dict[str, np.ndarray]:
-    """fp32 -> fp16 wire compression (reference: worker.py:264-268)."""
+    """fp32 -> fp16 wire compression (reference: worker.py:264-268).  Round-to-nearest-even, same bits as
+    ``astype(np.float16)``."""
     if how == "none":
         return {k: np.asarray(v, dtype=np.float32) for k, v in grads.items()}
-    return {k: np.asarray(v).astype(np.float16) for k, v in grads.items()}
+    _init_torch_map()
+    import torch
+    return {k: (_torch_cast(np.asarray(v), np.float16, torch.float16) if np.asarray(v).dtype.name in _NP2TORCH
+                else np.asarray(v).astype(np.float16)) for k, v in grads.items()}
 
 
 def decompress_gradients(grads: Mapping[str, np.ndarray]) -> Dict[str, np.ndarray]:
     """wire -> fp32 (reference: server.py:232-237)."""
-    return {k: np.asarray(v).astype(np.float32) for k, v in grads.items()}
+    _init_torch_map()
+    import torch
+    return {k: (_torch_cast(np.asarray(v), np.float32, torch.float32) if np.asarray(v).dtype.name in _NP2TORCH
+                else np.asarray(v).astype(np.float32)) for k, v in grads.items()}
