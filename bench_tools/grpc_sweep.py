@@ -74,8 +74,9 @@ def sweep_ours(reps: int):
             assert stub.PushGradrients(proto.PushRequest(worker_id=wid, gradients=payload, local_step=0)).received
 
         def pull():
-            rep = stub.FetchParameters(proto.FetchRequest(worker_id=wid))
-            arrs, _ = codec.decode_any(rep.parameters, allow_pickle=False)
+            raw = stub.FetchParametersRaw(proto.FetchRequest(worker_id=wid))     # what DistributedWorker does
+            payload, _ = proto.split_fetch_reply_wire(raw)
+            arrs, _ = codec.decode_any(payload, allow_pickle=False)
             return arrs["w"][:1].copy()
 
         rows.append({"payload_bytes": nbytes, "push_s": _time(push, reps), "pull_s": _time(pull, reps)})

@@ -119,9 +119,15 @@ class DistributedWorker:
     # ------------------------------------------------------------------ pull / push
     def fetch_parameters(self) -> int:
         with self.timer.phase("pull"):
-            rep = self.stub.FetchParameters(proto.FetchRequest(worker_id=self.worker_id))
-            arrays, _ = codec.decode_any(rep.parameters, allow_pickle=self.cfg.compat_pickle)
-            self.global_step_cache = rep.global_step
+            req = proto.FetchRequest(worker_id=self.worker_id)
+            raw_call = getattr(self.stub, "FetchParametersRaw", None)
+            if raw_call is not None:              # zero-copy: no protobuf parse, no copy of the payload out of it
+                payload, step = proto.split_fetch_reply_wire(raw_call(req))
+            else:
+                rep = self.stub.FetchParameters(req)
+                payload, step = rep.parameters, rep.global_step
+            arrays, _ = codec.decode_any(payload, allow_pickle=self.cfg.compat_pickle)
+            self.global_step_cache = step
             sd = self.model.state_dict()
             keep_local_bn = self.cfg.bn_buffer_policy == "local" and self.local_step_counter > 0
             with torch.no_grad(), warnings.catch_warnings():
@@ -139,7 +145,7 @@ class DistributedWorker:
                         if arr.dtype.name in _TORCH_DTYPES and arr.flags.c_contiguous \
                         else torch.from_numpy(np.array(arr, copy=True))
                     dst.copy_(src)
-        return rep.global_step
+        return step
 
     def compress_gradients(self, grads: Dict[str, np.ndarray]) -> Dict[str, np.ndarray]:
         return codec.compress_gradients(grads, self.cfg.compress)

@@ -16,6 +16,8 @@ Public surface mirrors the generated code:
 """
 from __future__ import annotations
 
+from typing import Tuple
+
 import grpc
 from google.protobuf import descriptor_pb2, descriptor_pool, message_factory
 
@@ -91,8 +93,61 @@ def method_path(method: str) -> str:
     return f"/{SERVICE_NAME}/{method}"
 
 
+def _varint(n: int) -> bytes:
+    out = bytearray()
+    while True:
+        b = n & 0x7F
+        n >>= 7
+        if n:
+            out.append(b | 0x80)
+        else:
+            out.append(b)
+            return bytes(out)
+
+
+def encode_fetch_reply_wire(parameters: bytes, global_step: int) -> bytes:
+    """Serialized FetchReply{parameters = 1, global_step = 2} built with ONE copy of the payload (the generated
+    serializer copies it into the message and again into the output: 2 x 45 MB per pull)."""
+    return b"".join([b"\x0a", _varint(len(parameters)), parameters, b"\x10",
+                     _varint(global_step & 0xFFFFFFFFFFFFFFFF)])       # int32 is sign-extended to 64 bits on the wire
+
+
+def split_fetch_reply_wire(raw) -> Tuple[memoryview, int]:
+    """(zero-copy view of `parameters`, global_step) from a serialized FetchReply; falls back to the protobuf
+    parser for any layout other than the two known fields."""
+    mv = memoryview(raw)
+    pos, n = 0, len(mv)
+    params, step = memoryview(b""), 0
+    try:
+        while pos < n:
+            tag = mv[pos]
+            pos += 1
+            val, shift = 0, 0
+            while True:
+                b = mv[pos]
+                pos += 1
+                val |= (b & 0x7F) << shift
+                shift += 7
+                if not b & 0x80:
+                    break
+            if tag == 0x0A:
+                params = mv[pos:pos + val]
+                if len(params) != val:
+                    raise ValueError("truncated")
+                pos += val
+            elif tag == 0x10:
+                step = val - (1 << 64) if val >= (1 << 63) else val
+            else:
+                raise ValueError("unknown field")
+        return params, int(step)
+    except (ValueError, IndexError):
+        msg = _CLASSES["FetchReply"].FromString(bytes(raw))
+        return memoryview(msg.parameters), int(msg.global_step)
+
+
 class ParameterServerStub:
-    """Client stub; one unary-unary callable per RPC (same attribute names as generated code)."""
+    """Client stub; one unary-unary callable per RPC (same attribute names as generated code), plus
+    `FetchParametersRaw`: the same RPC with the reply left as raw bytes for `split_fetch_reply_wire`."""
 
     def __init__(self, channel: grpc.Channel):
         for meth, req, rep in METHODS:
@@ -101,6 +156,10 @@ class ParameterServerStub:
                 request_serializer=_CLASSES[req].SerializeToString,
                 response_deserializer=_CLASSES[rep].FromString,
             ))
+        self.FetchParametersRaw = channel.unary_unary(
+            method_path("FetchParameters"),
+            request_serializer=_CLASSES["FetchRequest"].SerializeToString,
+            response_deserializer=lambda b: b)
 
 
 class ParameterServerServicer:
@@ -127,10 +186,14 @@ class ParameterServerServicer:
 def add_ParameterServerServicer_to_server(servicer, server: grpc.Server) -> None:
     handlers = {}
     for meth, req, rep in METHODS:
+        fn, ser = getattr(servicer, meth), _CLASSES[rep].SerializeToString
+        wire = getattr(servicer, meth + "Wire", None)
+        if wire is not None:                      # handler that returns already-serialized reply bytes
+            fn, ser = wire, (lambda b: b)
         handlers[meth] = grpc.unary_unary_rpc_method_handler(
-            getattr(servicer, meth),
+            fn,
             request_deserializer=_CLASSES[req].FromString,
-            response_serializer=_CLASSES[rep].SerializeToString,
+            response_serializer=ser,
         )
     server.add_generic_rpc_handlers(
         (grpc.method_handlers_generic_handler(SERVICE_NAME, handlers),))

@@ -221,8 +221,8 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             if info is not None:
                 info["last_seen"] = time.time()
 
-    def FetchParameters(self, request, context):
-        self._touch(request.worker_id)
+    def _fetch_payload(self) -> tuple:
+        """(global_step, payload bytes, serialized FetchReply) of the current parameters, encoded once per update."""
         as_pickle = bool(self.cfg.compat_pickle)
         with self.param_lock:
             cached = self._fetch_cache.get(as_pickle)
@@ -231,12 +231,25 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 if self.cfg.pull_compress == "fp16" and not as_pickle:
                     # floating tensors travel as fp16 (the frame is self-describing; the worker casts back);
                     # integer buffers (num_batches_tracked) and the fp32 master here are untouched
-                    params = {k: (v.astype(np.float16) if v.dtype == np.float32 else v) for k, v in params.items()}
+                    params = codec.compress_gradients({k: v for k, v in params.items() if v.dtype == np.float32},
+                                                      "fp16") | {k: v for k, v in params.items()
+                                                                 if v.dtype != np.float32}
+                    params = {k: params[k] for k in self.parameters}          # keep the state_dict order
                 payload = codec.encode_any(params, as_pickle, {"global_step": self.global_step})
-                cached = (self.global_step, payload)
+                cached = (self.global_step, payload, proto.encode_fetch_reply_wire(payload, self.global_step))
                 self._fetch_cache[as_pickle] = cached
-            step, payload = cached
+            return cached
+
+    def FetchParameters(self, request, context):
+        self._touch(request.worker_id)
+        step, payload, _ = self._fetch_payload()
         return proto.FetchReply(parameters=payload, global_step=step)
+
+    def FetchParametersWire(self, request, context):
+        """Same RPC for the gRPC runtime: the reply is the cached, already-serialized message (every worker of a round
+        gets the same bytes; no per-request copy of the 45 MB payload on the server)."""
+        self._touch(request.worker_id)
+        return self._fetch_payload()[2]
 
     def PushGradrients(self, request, context):
         wid, local_step = request.worker_id, request.local_step

@@ -44,3 +44,20 @@ def test_proto_file_is_consistent_with_descriptors():
         assert re.search(rf"rpc {meth}\({req}\) returns \({rep}\)", text)
     fdp = proto.build_file_descriptor_proto()
     assert isinstance(fdp, descriptor_pb2.FileDescriptorProto) and fdp.package == ""
+
+
+def test_fetch_reply_wire_helpers_match_protobuf():
+    """encode_fetch_reply_wire / split_fetch_reply_wire are byte-compatible with the protobuf (and therefore with the
+    reference's generated FetchReply class)."""
+    from dps_b200.rpc import proto
+    payload = bytes(range(256)) * 300
+    for step in (0, 1, 127, 128, 300, 2 ** 31 - 1, -1):
+        wire = proto.encode_fetch_reply_wire(payload, step)
+        msg = proto.FetchReply.FromString(wire)
+        assert msg.parameters == payload and msg.global_step == step
+        view, got = proto.split_fetch_reply_wire(wire)
+        assert bytes(view) == payload and got == step
+        # the generated serializer's output (field 2 omitted when zero) splits the same way
+        view2, got2 = proto.split_fetch_reply_wire(proto.FetchReply(parameters=payload, global_step=step).SerializeToString())
+        assert bytes(view2) == payload and got2 == step
+    assert proto.split_fetch_reply_wire(b"") == (memoryview(b""), 0)
