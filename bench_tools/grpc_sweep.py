@@ -71,7 +71,7 @@ def sweep_ours(reps: int):
 
         def push():
             payload = codec.encode_any(codec.compress_gradients(g, "fp16"), False)
-            assert stub.PushGradrients(proto.PushRequest(worker_id=wid, gradients=payload, local_step=0)).received
+            assert stub.PushGradrientsRaw(proto.encode_push_request_wire(wid, payload, 0)).received   # as the client
 
         def pull():
             raw = stub.FetchParametersRaw(proto.FetchRequest(worker_id=wid))     # what DistributedWorker does

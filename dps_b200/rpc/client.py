@@ -161,8 +161,12 @@ class DistributedWorker:
                     tensors["buffer/" + n] = b.detach().cpu().numpy()
             payload = codec.encode_any(tensors, as_pickle, {"worker": self.worker_id})
             self.last_push_bytes = len(payload)
-            rep = self.stub.PushGradrients(proto.PushRequest(
-                worker_id=self.worker_id, gradients=payload, local_step=self.global_step_cache))
+            raw_call = getattr(self.stub, "PushGradrientsRaw", None)
+            if raw_call is not None:
+                rep = raw_call(proto.encode_push_request_wire(self.worker_id, payload, self.global_step_cache))
+            else:
+                rep = self.stub.PushGradrients(proto.PushRequest(
+                    worker_id=self.worker_id, gradients=payload, local_step=self.global_step_cache))
             if not rep.received:
                 self.rejected_pushes += 1
             return rep.received

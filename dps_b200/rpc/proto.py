@@ -145,6 +145,49 @@ def split_fetch_reply_wire(raw) -> Tuple[memoryview, int]:
         return memoryview(msg.parameters), int(msg.global_step)
 
 
+def encode_push_request_wire(worker_id: int, gradients: bytes, local_step: int) -> bytes:
+    """Serialized PushRequest{worker_id = 1, gradients = 2, local_step = 3} with one copy of the payload."""
+    return b"".join([b"\x08", _varint(worker_id & 0xFFFFFFFFFFFFFFFF), b"\x12", _varint(len(gradients)), gradients,
+                     b"\x18", _varint(local_step & 0xFFFFFFFFFFFFFFFF)])
+
+
+def split_push_request_wire(raw) -> Tuple[int, memoryview, int]:
+    """(worker_id, zero-copy view of `gradients`, local_step) from a serialized PushRequest (any field order;
+    unknown fields fall back to the protobuf parser)."""
+    mv = memoryview(raw)
+    pos, n = 0, len(mv)
+    wid, grads, step = 0, memoryview(b""), 0
+    try:
+        while pos < n:
+            tag = mv[pos]
+            pos += 1
+            val, shift = 0, 0
+            while True:
+                b = mv[pos]
+                pos += 1
+                val |= (b & 0x7F) << shift
+                shift += 7
+                if not b & 0x80:
+                    break
+            if tag == 0x12:
+                grads = mv[pos:pos + val]
+                if len(grads) != val:
+                    raise ValueError("truncated")
+                pos += val
+            elif tag in (0x08, 0x18):
+                val = val - (1 << 64) if val >= (1 << 63) else val
+                if tag == 0x08:
+                    wid = val
+                else:
+                    step = val
+            else:
+                raise ValueError("unknown field")
+        return int(wid), grads, int(step)
+    except (ValueError, IndexError):
+        msg = _CLASSES["PushRequest"].FromString(bytes(raw))
+        return int(msg.worker_id), memoryview(msg.gradients), int(msg.local_step)
+
+
 class ParameterServerStub:
     """Client stub; one unary-unary callable per RPC (same attribute names as generated code), plus
     `FetchParametersRaw`: the same RPC with the reply left as raw bytes for `split_fetch_reply_wire`."""
@@ -160,6 +203,11 @@ class ParameterServerStub:
             method_path("FetchParameters"),
             request_serializer=_CLASSES["FetchRequest"].SerializeToString,
             response_deserializer=lambda b: b)
+        # request = bytes from encode_push_request_wire (no copy of the payload into a message object)
+        self.PushGradrientsRaw = channel.unary_unary(
+            method_path("PushGradrients"),
+            request_serializer=lambda b: b,
+            response_deserializer=_CLASSES["PushReply"].FromString)
 
 
 class ParameterServerServicer:
@@ -186,15 +234,13 @@ class ParameterServerServicer:
 def add_ParameterServerServicer_to_server(servicer, server: grpc.Server) -> None:
     handlers = {}
     for meth, req, rep in METHODS:
-        fn, ser = getattr(servicer, meth), _CLASSES[rep].SerializeToString
+        fn, des, ser = getattr(servicer, meth), _CLASSES[req].FromString, _CLASSES[rep].SerializeToString
         wire = getattr(servicer, meth + "Wire", None)
-        if wire is not None:                      # handler that returns already-serialized reply bytes
+        if wire is not None and meth == "FetchParameters":      # handler returns already-serialized reply bytes
             fn, ser = wire, (lambda b: b)
-        handlers[meth] = grpc.unary_unary_rpc_method_handler(
-            fn,
-            request_deserializer=_CLASSES[req].FromString,
-            response_serializer=ser,
-        )
+        elif wire is not None and meth == "PushGradrients":     # handler takes the raw request bytes
+            fn, des = wire, (lambda b: b)
+        handlers[meth] = grpc.unary_unary_rpc_method_handler(fn, request_deserializer=des, response_serializer=ser)
     server.add_generic_rpc_handlers(
         (grpc.method_handlers_generic_handler(SERVICE_NAME, handlers),))
 

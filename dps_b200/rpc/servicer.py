@@ -252,9 +252,17 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         return self._fetch_payload()[2]
 
     def PushGradrients(self, request, context):
-        wid, local_step = request.worker_id, request.local_step
+        return self._push(request.worker_id, request.gradients, request.local_step)
+
+    def PushGradrientsWire(self, raw, context):
+        """Same RPC for the gRPC runtime: the request arrives as raw bytes and the 22 MB payload is used in place
+        (no protobuf parse, no copy out of the message)."""
+        wid, payload, local_step = proto.split_push_request_wire(raw)
+        return self._push(wid, payload, local_step)
+
+    def _push(self, wid: int, payload, local_step: int):
         try:
-            tensors, meta = codec.decode_any(request.gradients, allow_pickle=self.cfg.compat_pickle)
+            tensors, meta = codec.decode_any(payload, allow_pickle=self.cfg.compat_pickle)
         except Exception as e:  # malformed payload == reference's received=False path (server.py:260-262)
             self._log(f"Error processing gradients from worker {wid}: {e}")
             return proto.PushReply(received=False)

@@ -61,3 +61,15 @@ def test_fetch_reply_wire_helpers_match_protobuf():
         view2, got2 = proto.split_fetch_reply_wire(proto.FetchReply(parameters=payload, global_step=step).SerializeToString())
         assert bytes(view2) == payload and got2 == step
     assert proto.split_fetch_reply_wire(b"") == (memoryview(b""), 0)
+
+
+def test_push_request_wire_helpers_match_protobuf():
+    from dps_b200.rpc import proto
+    payload = bytes(range(251)) * 100
+    for wid, step in ((0, 0), (3, 7), (31, 2 ** 31 - 1), (200, 128), (1, -1)):
+        wire = proto.encode_push_request_wire(wid, payload, step)
+        msg = proto.PushRequest.FromString(wire)
+        assert (msg.worker_id, msg.gradients, msg.local_step) == (wid, payload, step)
+        for w in (wire, proto.PushRequest(worker_id=wid, gradients=payload, local_step=step).SerializeToString()):
+            got_wid, view, got_step = proto.split_push_request_wire(w)
+            assert (got_wid, bytes(view), got_step) == (wid, payload, step)
