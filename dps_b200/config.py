@@ -73,6 +73,7 @@ class Config:
     # ---- outputs -----------------------------------------------------------
     metrics_dir: Optional[str] = None     # write METRICS_JSON records to files here
     checkpoint: Optional[str] = None
+    checkpoint_every: int = 0             # gRPC server: also save every N global steps (0 = only at job end)
     resume: Optional[str] = None
     inject_fault: Optional[str] = None    # "rank:step" test hook
 
@@ -150,6 +151,7 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
                    help="gRPC/CPU worker: bf16 autocast + channels_last for the local step (master weights stay fp32)")
     p.add_argument("--metrics-dir", default=None)
     p.add_argument("--checkpoint", default=None)
+    p.add_argument("--checkpoint-every", type=int, default=0)
     p.add_argument("--resume", default=None)
     p.add_argument("--inject-fault", default=None)
 

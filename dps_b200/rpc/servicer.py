@@ -126,9 +126,18 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             from ..models.resnet import build_model
             model = build_model(cfg.num_classes, seed=cfg.seed)
             initial_state = {k: v.detach().cpu().numpy() for k, v in model.state_dict().items()}
+        resume_side: dict = {}
+        if cfg.resume:                     # PS recovery: the reference loses the model when the server restarts
+            from ..utils import checkpoint as CK
+            sd, resume_side = CK.load(cfg.resume)
+            initial_state = CK.to_numpy_state(sd)
         self.parameters: Dict[str, np.ndarray] = {k: np.array(v, copy=True) for k, v in initial_state.items()}
         self.param_lock = threading.Lock()
         self.opt = HostOptimizer(self.parameters, cfg.lr, cfg.momentum, cfg.weight_decay)
+        for k, v in (resume_side.get("momentum") or {}).items():
+            self.opt.velocity[k] = np.array(v.numpy() if hasattr(v, "numpy") else v, dtype=np.float32, copy=True)
+        self._resume_step = int(resume_side.get("global_step", 0))
+        self._last_ckpt_step = self._resume_step
 
         # membership
         self.registration_lock = threading.Lock()
@@ -139,7 +148,7 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         self.membership_epoch = 0
 
         # training state
-        self.global_step = 0
+        self.global_step = self._resume_step
         self.total_updates = 0
         self.gradients_processed = 0
         self.stats_lock = threading.Lock()
@@ -174,7 +183,29 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             self.global_step += 1
             self.total_updates += 1
             self._fetch_cache.clear()
+            due = (self.cfg.checkpoint and self.cfg.checkpoint_every > 0
+                   and self.global_step - self._last_ckpt_step >= self.cfg.checkpoint_every)
         self.update_times.append(time.time() - t0)
+        if due:
+            self.save_checkpoint()
+
+    def save_checkpoint(self, path: Optional[str] = None) -> Optional[str]:
+        """state_dict-compatible checkpoint (loads into the reference ResNet18 with strict=True) + resume sidecar
+        (global step, momentum, config).  The snapshot is taken under the parameter lock, the file is written
+        outside it and renamed into place."""
+        path = path or self.cfg.checkpoint
+        if not path:
+            return None
+        from ..utils import checkpoint as CK
+        with self.param_lock:
+            state = {k: np.array(v, copy=True) for k, v in self.parameters.items()}
+            mom = {k: np.array(v, copy=True) for k, v in self.opt.velocity.items()}
+            step = self.global_step
+            self._last_ckpt_step = step
+        CK.save(path, state, global_step=step, momentum=mom, config=self.cfg.to_dict(),
+                extra={"mode": self.mode, "total_updates": self.total_updates})
+        self._log(f"checkpoint written to {path} at global step {step}")
+        return path
 
     def aggregate_gradients_sync(self, worker_gradients: List[Dict[str, np.ndarray]]):
         return mean_gradients(worker_gradients)
@@ -368,6 +399,8 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 self._final_emitted = emit = True
         if emit:
             self._print_final_statistics()
+            if self.cfg.checkpoint:
+                self.save_checkpoint()
         return proto.JobFinishedReply(message="Acknowledged")
 
     # liveness -------------------------------------------------

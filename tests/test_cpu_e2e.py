@@ -134,3 +134,48 @@ def test_pull_compress_fp16_halves_payload_and_keeps_fp32_master(tmp_path):
     got = w.model.state_dict()["conv1.weight"]
     assert got.dtype == torch.float32
     assert torch.allclose(got, torch.from_numpy(sv.parameters["conv1.weight"]), atol=1e-3)
+
+
+def test_server_checkpoint_and_resume(tmp_path, ref_modules):
+    """PS recovery on the gRPC path: the reference loses the model when the server restarts.
+    Here the server writes a state_dict-compatible checkpoint (periodically and at job end) and a restarted server
+    resumes parameters, momentum and the global step from it."""
+    from dps_b200.rpc import codec, proto
+    from dps_b200.utils import checkpoint as CK
+    ck = str(tmp_path / "ps.pt")
+    cfg = Config(mode="sync", workers=1, lr=0.05, momentum=0.9, checkpoint=ck, checkpoint_every=2)
+    sv = S.ParameterServerServicer("sync", 1, 0.05, config=cfg)
+    wid = sv.RegisterWorker(proto.RegisterRequest(worker_ip="a"), None).worker_id
+    rng = np.random.default_rng(0)
+    names = [k for k, v in sv.parameters.items() if v.dtype == np.float32 and "running" not in k]
+
+    def push(server, step):
+        g = {k: (rng.normal(size=server.parameters[k].shape) * 1e-2).astype(np.float32) for k in names}
+        payload = codec.encode_any(codec.compress_gradients(g, "fp16"), False)
+        assert server.PushGradrients(proto.PushRequest(worker_id=wid, gradients=payload, local_step=step), None).received
+        return g
+
+    for s in range(3):
+        push(sv, s)
+    # periodic checkpoint after step 2; the file loads into the REFERENCE model, strict
+    sd, side = CK.load(ck)
+    assert side["global_step"] == 2 and set(side["momentum"]) == set(names)
+    ref_model = ref_modules["server"].ResNet18(num_classes=100)
+    ref_model.load_state_dict(sd, strict=True)
+    sv.JobFinished(proto.JobFinishedRequest(worker_id=wid), None)          # final checkpoint at job end
+    sd, side = CK.load(ck)
+    assert side["global_step"] == 3
+    # restart: same parameters, momentum and step; the next update equals the un-interrupted server's
+    sv2 = S.ParameterServerServicer("sync", 1, 0.05, config=cfg.replace(resume=ck, checkpoint=None))
+    assert sv2.global_step == 3
+    for k in names[:5]:
+        assert np.array_equal(sv2.parameters[k], sv.parameters[k])
+        assert np.array_equal(sv2.opt.velocity[k], sv.opt.velocity[k])
+    sv2.RegisterWorker(proto.RegisterRequest(worker_ip="a"), None)
+    state = rng.bit_generator.state
+    push(sv, 3)
+    rng.bit_generator.state = state                                        # the same gradient for the resumed server
+    push(sv2, 3)
+    assert sv2.global_step == sv.global_step == 4
+    for k in names[:5]:
+        assert np.array_equal(sv2.parameters[k], sv.parameters[k]), k
