@@ -53,6 +53,7 @@ class Config:
     # ---- behaviour switches ---------------------------
     nonblocking_sync: bool = False        # True = reference Q1 behaviour (RPC never blocks)
     barrier_timeout_s: float = 60.0       # Q3 fix: sync barrier timeout (drop missing ranks)
+    worker_timeout_s: float = 0.0         # gRPC server: evict workers silent for this long (0 = off; clients beat every 30 s)
     bn_buffer_policy: str = "mean"        # 'reference' | 'local' | 'mean'   (Q5)
     compat_pickle: bool = False           # accept/emit reference pickle payloads (Q15)
     compress: str = "fp16"                # gradient wire format: 'fp16' | 'none'
@@ -143,6 +144,7 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--local-step-policy", choices=["reference", "accumulate"], default="accumulate")
     p.add_argument("--nonblocking-sync", action="store_true")
     p.add_argument("--barrier-timeout-s", type=float, default=60.0)
+    p.add_argument("--worker-timeout-s", type=float, default=0.0)
     p.add_argument("--compat-pickle", action="store_true")
     p.add_argument("--compress", choices=["fp16", "none"], default="fp16")
     p.add_argument("--pull-compress", choices=["none", "fp16"], default="none",

@@ -145,7 +145,10 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         self.registered_workers_count = 0
         self.active_workers: set = set()
         self._free_ids: List[int] = []
+        self._departed: set = set()        # ids that finished or were evicted: the sync barrier does not wait for them
         self.membership_epoch = 0
+        self._monitor: Optional[threading.Thread] = None
+        self._monitor_stop = threading.Event()
 
         # training state
         self.global_step = self._resume_step
@@ -241,6 +244,7 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             self.registered_workers[wid] = {"worker_id": wid, "worker_ip": request.worker_ip,
                                             "registered_at": now, "last_seen": now}
             self.active_workers.add(wid)
+            self._departed.discard(wid)
             self.membership_epoch += 1
         self._log(f"[RegisterWorker] Worker {wid} from {request.worker_ip} registered "
                   f"({len(self.active_workers)}/{self.total_workers})")
@@ -310,7 +314,9 @@ class ParameterServerServicer(proto.ParameterServerServicer):
 
     # sync -----------------------------------------------------------------
     def _expected(self) -> int:
-        return self.total_workers
+        """Contributions a sync round waits for: W minus the workers that have left (finished their partition, or
+        were evicted as dead) and not come back.  The reference waits for W arrivals forever (Q3)."""
+        return max(1, self.total_workers - len(self._departed))
 
     def _complete_round_locked(self) -> None:
         sets = list(self.pending_gradients.values())
@@ -339,6 +345,9 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 return True
             deadline = (self.round_started_at or time.time()) + self.cfg.barrier_timeout_s
             while self.round_id == my_round:
+                if len(self.pending_gradients) >= self._expected():     # somebody left while we were waiting
+                    self._complete_round_locked()
+                    break
                 left = deadline - time.time()
                 if left <= 0:                               # Q3: proceed with the ranks present
                     if self.round_id == my_round:
@@ -394,9 +403,12 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 self.active_workers.discard(wid)
                 self._free_ids.append(wid)
                 self._free_ids.sort()
+                self._departed.add(wid)
                 self.membership_epoch += 1
             if not self.active_workers and not self._final_emitted:
                 self._final_emitted = emit = True
+        with self.sync_cv:                       # a round may now be complete without this worker
+            self.sync_cv.notify_all()
         if emit:
             self._print_final_statistics()
             if self.cfg.checkpoint:
@@ -417,9 +429,30 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 self.active_workers.discard(wid)
                 self._free_ids.append(wid)
                 self._free_ids.sort()
+                self._departed.add(wid)
                 self.membership_epoch += 1
         with self.sync_cv:
             self.sync_cv.notify_all()
+
+    def start_monitor(self, period_s: Optional[float] = None) -> None:
+        """Liveness watchdog (the reference writes `last_seen` on every RPC and never reads it, server.py:200): evict
+        workers that have been silent for `worker_timeout_s`; their id and partition become available again."""
+        timeout = self.cfg.worker_timeout_s
+        if timeout <= 0 or self._monitor is not None:
+            return
+        period = period_s if period_s is not None else max(0.05, min(5.0, timeout / 3.0))
+
+        def loop():
+            while not self._monitor_stop.wait(period):
+                for w in self.stale_workers(timeout):
+                    self._log(f"worker {w} silent for more than {timeout:.1f}s: evicted")
+                    self.evict(w)
+
+        self._monitor = threading.Thread(target=loop, daemon=True, name="dps-liveness")
+        self._monitor.start()
+
+    def stop_monitor(self) -> None:
+        self._monitor_stop.set()
 
     # metrics --------------------------------------------------------------
     def server_metrics(self) -> dict:
@@ -468,6 +501,7 @@ def build_server(cfg: Config, servicer: Optional[ParameterServerServicer] = None
     server = grpc.server(pool, options=proto.GRPC_OPTIONS)
     proto.add_ParameterServerServicer_to_server(servicer, server)
     port = server.add_insecure_port(f"{bind}:{cfg.port}")
+    servicer.start_monitor()
     return server, servicer, port
 
 

@@ -125,3 +125,51 @@ def test_final_metrics_emitted_once_q11(capsys):
     ours.JobFinished(proto.JobFinishedRequest(worker_id=wid), None)
     out = capsys.readouterr().out
     assert out.count("METRICS_JSON:") == 1 and "SERVER_FINAL_METRICS" in out
+
+
+def test_finished_worker_does_not_stall_the_barrier():
+    """Uneven partitions: a worker that has sent JobFinished is no longer waited for (the true barrier would
+    otherwise time out on every remaining round of the others)."""
+    import threading
+    import time
+    ours = S.ParameterServerServicer("sync", 2, 0.1, initial_state=_small_state(),
+                                     config=Config(barrier_timeout_s=30.0))
+    a = ours.RegisterWorker(proto.RegisterRequest(worker_ip="a"), None).worker_id
+    b = ours.RegisterWorker(proto.RegisterRequest(worker_ip="b"), None).worker_id
+    g = _grads(1, _small_state())
+    # b leaves while a is already waiting in the barrier: a's round completes at once
+    done = []
+    th = threading.Thread(target=lambda: done.append(ours._handle_sync_gradients(a, g, 0)))
+    th.start()
+    time.sleep(0.1)
+    assert th.is_alive()
+    t0 = time.time()
+    ours.JobFinished(proto.JobFinishedRequest(worker_id=b), None)
+    th.join(5.0)
+    assert done == [True] and ours.global_step == 1 and ours.barrier_timeouts == 0 and time.time() - t0 < 2.0
+    # and later rounds of a complete immediately
+    t0 = time.time()
+    assert ours._handle_sync_gradients(a, g, 1) and ours.global_step == 2 and time.time() - t0 < 1.0
+
+
+def test_liveness_monitor_evicts_silent_worker_and_readmits_it():
+    import time
+    ours = S.ParameterServerServicer("sync", 2, 0.1, initial_state=_small_state(),
+                                     config=Config(barrier_timeout_s=30.0, worker_timeout_s=0.3))
+    a = ours.RegisterWorker(proto.RegisterRequest(worker_ip="a"), None).worker_id
+    b = ours.RegisterWorker(proto.RegisterRequest(worker_ip="b"), None).worker_id
+    ours.start_monitor(period_s=0.05)
+    try:
+        g = _grads(1, _small_state())
+        deadline = time.time() + 3.0
+        while b in ours.active_workers and time.time() < deadline:
+            ours._touch(a)                                   # a keeps talking, b is silent
+            time.sleep(0.05)
+        assert b not in ours.active_workers and a in ours.active_workers and ours._expected() == 1
+        t0 = time.time()
+        assert ours._handle_sync_gradients(a, g, 0) and ours.global_step == 1 and time.time() - t0 < 1.0
+        # the evicted worker comes back: same id (same data partition), and the barrier waits for it again
+        again = ours.RegisterWorker(proto.RegisterRequest(worker_ip="b2"), None).worker_id
+        assert again == b and ours._expected() == 2
+    finally:
+        ours.stop_monitor()
