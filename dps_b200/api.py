@@ -458,14 +458,27 @@ class Worker:
             self._build_graph()                             # one-time capture is set-up, not epoch time
         self.training_start_time = time.time()
         epochs = self.cfg.epochs if epochs is None else epochs
+        # Sync mode is a true barrier: every rank must take the same number of steps per epoch.  The last worker's
+        # partition also holds the remainder (reference: worker.py:166-179) and can contain one more full batch.
+        per_epoch = None
+        if self.world > 1 and self.cfg.mode == "sync" and all(hasattr(train_loader, a) for a in ("start", "end")):
+            import torch.distributed as dist
+            t = torch.tensor([(train_loader.end - train_loader.start) // self.cfg.batch_size],
+                             device=self.job.device, dtype=torch.int64)
+            dist.all_reduce(t, op=dist.ReduceOp.MIN)
+            per_epoch = int(t.item())
         done = False
         last = None
         for _ in range(epochs):
             t0 = time.time()
+            taken = 0
             for x, y in train_loader:
                 if int(y.numel()) != self.cfg.batch_size:
                     continue                                # static shapes: drop the ragged tail batch
+                if per_epoch is not None and taken >= per_epoch:
+                    break
                 last = self.train_step(x, y)
+                taken += 1
                 if max_steps is not None and self.local_step_counter >= max_steps:
                     done = True
                     break
