@@ -36,6 +36,10 @@ _TORCH_DTYPES = {"float32": torch.float32, "float16": torch.float16, "float64": 
                  "bool": torch.bool, "int16": torch.int16}
 
 
+class SimulatedCrash(RuntimeError):
+    """Raised by the --inject-fault test hook."""
+
+
 class DistributedWorker:
     def __init__(self, server_address: str = "localhost:8000", worker_name: str = "worker-node",
                  config: Optional[Config] = None, verbose: bool = False):
@@ -197,6 +201,11 @@ class DistributedWorker:
     # ------------------------------------------------------------------ loop
     def run_training(self, evaluate: bool = True, eval_batches: Optional[int] = None) -> None:
         self.training_start_time = time.time()
+        self._crashed, self._fault_step = False, None
+        if self.cfg.inject_fault:
+            fid, fstep = self.cfg.inject_fault.split(":")
+            if int(fid) == self.worker_id:
+                self._fault_step = int(fstep)
         k = max(1, self.local_steps_per_sync)
         accumulate = self.cfg.local_step_policy == "accumulate"
         try:
@@ -222,13 +231,22 @@ class DistributedWorker:
                     if self.max_steps is not None and self.local_step_counter >= self.max_steps:
                         done = True
                         break
+                    if self._fault_step is not None and self.local_step_counter >= self._fault_step:
+                        # test hook (--inject-fault id:step): die like a killed process -- no JobFinished,
+                        # no more heartbeats; the server's barrier timeout / liveness monitor must cope
+                        self._crashed = True
+                        self.training_active = False
+                        raise SimulatedCrash(f"worker {self.worker_id} injected fault at step {self._fault_step}")
                 self.epoch_times.append(time.time() - t0)   # excludes evaluation (Q17)
                 if evaluate:
                     self.evaluate_model(eval_batches)
                 if done:
                     break
         finally:
-            self.cleanup()
+            if not self._crashed:
+                self.cleanup()
+            elif self.channel is not None:
+                self.channel.close()
             self.print_worker_statistics()
 
     def print_worker_statistics(self) -> dict:

@@ -146,6 +146,7 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         self.active_workers: set = set()
         self._free_ids: List[int] = []
         self._departed: set = set()        # ids that finished or were evicted: the sync barrier does not wait for them
+        self._evicted: set = set()         # evicted as silent; revived by their next RPC if the id is still free
         self.membership_epoch = 0
         self._monitor: Optional[threading.Thread] = None
         self._monitor_stop = threading.Event()
@@ -245,6 +246,7 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                                             "registered_at": now, "last_seen": now}
             self.active_workers.add(wid)
             self._departed.discard(wid)
+            self._evicted.discard(wid)
             self.membership_epoch += 1
         self._log(f"[RegisterWorker] Worker {wid} from {request.worker_ip} registered "
                   f"({len(self.active_workers)}/{self.total_workers})")
@@ -255,6 +257,13 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             info = self.registered_workers.get(wid)
             if info is not None:
                 info["last_seen"] = time.time()
+                if wid in self._evicted and wid in self._free_ids:
+                    # it was only slow, not dead, and nobody took its slot meanwhile: back in
+                    self._evicted.discard(wid)
+                    self._free_ids.remove(wid)
+                    self._departed.discard(wid)
+                    self.active_workers.add(wid)
+                    self.membership_epoch += 1
 
     def _fetch_payload(self) -> tuple:
         """(global_step, payload bytes, serialized FetchReply) of the current parameters, encoded once per update."""
@@ -430,6 +439,7 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 self._free_ids.append(wid)
                 self._free_ids.sort()
                 self._departed.add(wid)
+                self._evicted.add(wid)
                 self.membership_epoch += 1
         with self.sync_cv:
             self.sync_cv.notify_all()

@@ -179,3 +179,43 @@ def test_server_checkpoint_and_resume(tmp_path, ref_modules):
     assert sv2.global_step == sv.global_step == 4
     for k in names[:5]:
         assert np.array_equal(sv2.parameters[k], sv.parameters[k]), k
+
+
+def test_injected_worker_crash_is_survived_on_the_grpc_path(tmp_path):
+    """kill a rank mid-job.  Worker 1 dies after its first step without JobFinished; the server's
+    liveness monitor evicts it (or the barrier times out once) and worker 0 finishes all its steps."""
+    import time
+    from dps_b200.rpc.client import SimulatedCrash
+    torch.set_num_threads(2)
+    cfg = Config(mode="sync", workers=2, lr=0.05, batch_size=8, epochs=1, train_samples=64, test_samples=8,
+                 barrier_timeout_s=20.0, worker_timeout_s=2.5, inject_fault="1:1")
+    server, sv, port = S.build_server(cfg.replace(port=0), bind="127.0.0.1")
+    server.start()
+    out = {}
+
+    def run(i):
+        w = DistributedWorker(f"127.0.0.1:{port}", f"w{i}", config=cfg)
+        try:
+            w.connect_to_server()
+            w.setup_model()
+            w.setup_data()
+            out[w.worker_id] = w
+            w.run_training(evaluate=False)
+        except SimulatedCrash:
+            out["crashed"] = w.worker_id
+        except Exception as e:  # pragma: no cover
+            out["error"] = e
+
+    ths = [threading.Thread(target=run, args=(i,)) for i in range(2)]
+    t0 = time.time()
+    [t.start() for t in ths]
+    [t.join(120) for t in ths]
+    sv.stop_monitor()
+    server.stop(0)
+    assert "error" not in out, out.get("error")
+    assert out.get("crashed") == 1
+    survivor = out[0]
+    assert survivor.local_step_counter == 4                       # its whole partition: 32 samples / 8
+    assert sv.global_step == 4 and 1 not in sv.active_workers
+    assert sv.barrier_timeouts <= 1                               # eviction, not a timeout per round
+    assert time.time() - t0 < 60

@@ -173,3 +173,18 @@ def test_liveness_monitor_evicts_silent_worker_and_readmits_it():
         assert again == b and ours._expected() == 2
     finally:
         ours.stop_monitor()
+
+
+def test_evicted_but_alive_worker_is_revived_by_its_next_rpc():
+    ours = S.ParameterServerServicer("sync", 2, 0.1, initial_state=_small_state(), config=Config(barrier_timeout_s=5.0))
+    a = ours.RegisterWorker(proto.RegisterRequest(worker_ip="a"), None).worker_id
+    b = ours.RegisterWorker(proto.RegisterRequest(worker_ip="b"), None).worker_id
+    ours.evict(b)
+    assert ours._expected() == 1 and b not in ours.active_workers
+    ours.FetchParameters(proto.FetchRequest(worker_id=b), None)           # b was only slow
+    assert b in ours.active_workers and ours._expected() == 2 and b not in ours._free_ids
+    # ... unless its slot was handed to a replacement in the meantime
+    ours.evict(b)
+    c = ours.RegisterWorker(proto.RegisterRequest(worker_ip="c"), None).worker_id
+    assert c == b
+    assert ours._expected() == 2
