@@ -165,6 +165,7 @@ def test_liveness_monitor_evicts_silent_worker_and_readmits_it():
         while b in ours.active_workers and time.time() < deadline:
             ours._touch(a)                                   # a keeps talking, b is silent
             time.sleep(0.05)
+        ours._touch(a)                                       # (revives a if a stalled test process let it lapse too)
         assert b not in ours.active_workers and a in ours.active_workers and ours._expected() == 1
         t0 = time.time()
         assert ours._handle_sync_gradients(a, g, 0) and ours.global_step == 1 and time.time() - t0 < 1.0
