@@ -41,7 +41,8 @@ def parse_args(argv=None):
     p.add_argument("--mode", choices=["sync", "async"], default="sync")
     p.add_argument("--batch", type=int, default=128)
     p.add_argument("--image-size", type=int, default=32)
-    p.add_argument("--engine", choices=["native", "torch"], default="native")
+    p.add_argument("--engine", choices=["native", "torch"], default="native",
+                   help="torch = BASELINE arm: same PS kernels, ATen/cuDNN compute (bench_tools/torch_engine.py)")
     p.add_argument("--momentum", type=float, default=0.0)
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="eager launches (for ncu launch lists)")
@@ -104,9 +105,12 @@ def run_ours(args) -> dict:
     local = int(os.environ.get("LOCAL_RANK", rank))
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     cfg = Config(mode=args.mode, workers=world, batch_size=args.batch, lr=0.1, momentum=args.momentum,
-                 image_size=args.image_size, engine=args.engine, barrier_timeout_s=30.0,
+                 image_size=args.image_size, barrier_timeout_s=30.0,
                  use_cuda_graph=not args.no_graph)
-    job = Job(cfg, rank=rank, world=world, device_index=local)
+    factory = None
+    if args.engine == "torch":
+        from bench_tools.torch_engine import TorchEngine as factory
+    job = Job(cfg, rank=rank, world=world, device_index=local, engine_factory=factory)
     wk, dev = job.worker, job.device
     B, S = args.batch, args.image_size
     K, W = args.steps, max(3, args.warmup)

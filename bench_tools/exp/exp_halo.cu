@@ -4,7 +4,9 @@
 // stride-byte-offset of (BW+2)*128 B between 8-row groups (BW == 8, so one image row == one 8-row group).
 // variant 0: base_offset field = 0;  variant 1: base_offset = (start_address >> 7) & 7.
 #include "common.cuh"
-#include "../include/dps_b200_compute.h"
+// build (not part of libdps_b200.so): nvcc -gencode arch=compute_100a,code=sm_100a -O3 -std=c++17 -shared -Xcompiler -fPIC \
+//   -I csrc -I include -o bench_tools/bin/libexp_halo.so bench_tools/exp/exp_halo.cu
+thread_local char g_dps_err[512];
 
 namespace dps {
 

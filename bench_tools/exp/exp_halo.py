@@ -1,9 +1,12 @@
-"""Hardware probe: shifted-window A operand from a shared-memory halo tile (see csrc/exp_halo.cu)."""
+"""Hardware probe: shifted-window A operand from a shared-memory halo tile (see bench_tools/exp/exp_halo.cu;
+built separately into bench_tools/bin/libexp_halo.so, not part of the product library)."""
 import ctypes as C, os, sys
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
 import torch, torch.nn.functional as F
 from dps_b200.ops import _lib as L
-lib = L.lib()
+L.lib()
+lib = C.CDLL(os.path.join(ROOT, "bench_tools", "bin", "libexp_halo.so"))
 lib.dps_exp_halo_tile.restype = C.c_int
 lib.dps_exp_halo_tile.argtypes = [C.c_void_p] * 3 + [C.c_int] * 7 + [C.c_void_p]
 N, H, W = 2, 32, 32

@@ -1,6 +1,5 @@
-"""ATen/cuDNN execution of the same network over the same arenas (``engine='torch'``).
-
-Not the product path: it is the portable fallback and the apples-to-apples compute baseline for the
+"""BASELINE (not product code): ATen/cuDNN execution of the same network over the same arenas, injected with
+``Job(cfg, engine_factory=TorchEngine)``.  It is the apples-to-apples compute baseline for the
 native engine (same Push/Pull kernels, library convolutions instead of the tcgen05 ones).  Parameters
 are fp32 views refreshed from the pulled bf16 arena; ``.grad`` tensors are strided views INTO the flat
 fp32 gradient arena, so autograd accumulates straight into what the Push kernel sends.
@@ -13,7 +12,7 @@ from typing import Dict, Optional
 import torch
 from torch import nn
 
-from ..store.shardmap import Layout
+from dps_b200.store.shardmap import Layout
 
 
 class TorchEngine:

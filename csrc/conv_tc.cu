@@ -119,24 +119,25 @@ __device__ __forceinline__ void red_fixed(long long* dst, float v, float scale) 
   atomicAdd(reinterpret_cast<unsigned long long*>(dst), (unsigned long long)__float2ll_rn(v * scale));
 }
 
-// Epilogue shared by the conv kernels, executed by EPI_WARPS warps (threads 64 .. 64+32*EPI_WARPS):
+// Epilogue shared by the conv kernels, executed by EPI_WARPS warps (threads et0 .. et0+32*EPI_WARPS, named barrier BAR;
+// persistent kernels run two such groups side by side, one per TMEM accumulator):
 // TMEM accumulator -> bf16 staging tile -> (BN statistics | addend + fused BN-backward reduction) -> coalesced stores.
 // Warp w may only read TMEM lanes of quadrant (w & 3); with 8 warps each quadrant is split in two column halves.
-template <int BLOCK_N, int EPI_WARPS>
+template <int BLOCK_N, int EPI_WARPS, int MAX_GROUP = 4>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int n0, int h0, int w0, int c_out0,
                                               uint32_t stage, uint32_t tmem_acc, uint64_t* tmem_full,
-                                              uint32_t full_parity, uint64_t* tmem_empty) {
+                                              uint32_t full_parity, uint64_t* tmem_empty, int et0 = 64, int bar_id = 1) {
   constexpr int T = EPI_WARPS * 32;
   constexpr int kPitch = ConvSmem<BLOCK_N>::kPitch;
   constexpr int kChunks = BLOCK_N / 8;                  // 16-byte chunks per row
   constexpr int kRowsPerPass = T / kChunks;
   constexpr int kPasses = kTileM / kRowsPerPass;
-  constexpr int kGroup = kPasses < 4 ? kPasses : 4;
+  constexpr int kGroup = kPasses < MAX_GROUP ? kPasses : MAX_GROUP;   // rows prefetched together (12 registers each)
   constexpr int kColsPerWarp = BLOCK_N / (EPI_WARPS / 4);
   constexpr int kPairs = BLOCK_N / 2;                   // reductions work on bf16 pairs
   constexpr int kParts = T / kPairs;                    // row partitions of the column reductions
   constexpr int kRowsPerPart = kTileM / kParts;
-  const int et = threadIdx.x - 64;
+  const int et = threadIdx.x - et0;          // index inside this epilogue group
   const int ew = et >> 5, lane = et & 31;
   const int q = (threadIdx.x >> 5) & 3;                 // TMEM lane quadrant of this warp
   const int row = q * 32 + lane;                        // tile row == pixel index in the box
@@ -214,7 +215,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
     __syncwarp();
     if (lane == 0) mbar_arrive(tmem_empty);
   }
-  asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");      // epilogue warps only
+  asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(T) : "memory");      // epilogue warps only
 
   const int pair = et % kPairs, part = et / kPairs;
   // deterministic two-level column reduction: per-thread partial over its rows -> shared -> fixed-order sum ->
@@ -224,7 +225,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
     sts_f32(part_s + ((part * 4 + 1) * kPairs + pair) * 4, a1);
     sts_f32(part_s + ((part * 4 + 2) * kPairs + pair) * 4, b0);
     sts_f32(part_s + ((part * 4 + 3) * kPairs + pair) * 4, b1);
-    asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(T) : "memory");
     for (int idx = et; idx < 2 * BLOCK_N; idx += T) {
       const int which = idx / BLOCK_N, ch = idx % BLOCK_N;
       const int k = which * 2 + (ch & 1), pr = ch >> 1;
@@ -280,7 +281,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
     }
   }
   if (fuse) {
-    asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");
+    asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(T) : "memory");
     const float mu0 = p.fuse_mean[c_out0 + 2 * pair], mu1 = p.fuse_mean[c_out0 + 2 * pair + 1];
     const float rs0 = p.fuse_rstd[c_out0 + 2 * pair], rs1 = p.fuse_rstd[c_out0 + 2 * pair + 1];
     float d0 = 0.f, d1 = 0.f, x0 = 0.f, x1 = 0.f;
@@ -295,7 +296,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
     }
     reduce_store(d0, d1, x0, x1, p.fuse_sums, p.out_C, (float)kGradSumScale, (float)kGradSumScale);
   }
-  if (tmem_empty != nullptr) asm volatile("bar.sync 1, %0;" ::"n"(T) : "memory");   // staging is reused by the next tile
+  if (tmem_empty != nullptr) asm volatile("bar.sync %0, %1;" ::"r"(bar_id), "n"(T) : "memory");   // staging is reused by the next tile
 }
 
 // Register-reduction variant of the epilogue: ONE staging tile instead of two.  The column reductions (BN statistics,
@@ -543,31 +544,39 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
 
   if (warp == 0) {
     // ===================== TMA producer =====================
+    // The issue loops of the producer and of the MMA thread are single-thread critical paths (one iteration per
+    // 64-deep reduction block): no integer divisions and no parameter-space loads inside them -- stage / phase are
+    // running counters and the tap is fetched once per tap.  (Measured with bench_tools/exp/ingest_probe.cu: one
+    // thread sustains a TMA every ~160 cycles and an SM ingests ~100 B/clk; the division-based loops of the first
+    // version needed 800-1100 cycles per block and capped every tap-loop conv at ~31 B/clk per SM.)
     if (elect_one()) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % nst, ph = (kb / nst) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        const Tap tp = p.taps[grp][kb / p.red_blocks];
-        const int cb = kb % p.red_blocks;
-        uint8_t* a = stages + s * S::kStageBytes;
-        uint8_t* b = a + kABytes;
-        mbar_expect_tx(&full[s], S::kStageBytes);
-        if (CL == 1) {
-          tma_load_5d(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
-        } else {
-          // my 128/CL rows of the box (tile order: w fastest, then h, then n), multicast to the whole cluster
-          const int q = (int)cluster_ctarank();
-          const int base = (q * (kTileM / CL)) >> p.bw_sh;          // first (h, n) line of my slice
-          const int bh_sh = p.bhw_sh - p.bw_sh;
-          tma_load_5d_mc(a + q * (kTileM / CL) * 128, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph,
-                         h0 + tp.da + (base & ((1 << bh_sh) - 1)), n0 + (base >> bh_sh), kClusterMask);
-        }
-        if (!B_MN) {
-          tma_load_2d(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0);
-        } else {
+      int s = 0;
+      uint32_t ph = 0;
+      const int red_blocks = p.red_blocks;
+      // cluster variant: my 128/CL rows of the box (tile order: w fastest, then h, then n)
+      const int q = (CL > 1) ? (int)cluster_ctarank() : 0;
+      const int base = (q * (kTileM / CL)) >> p.bw_sh;              // first (h, n) line of my slice
+      const int bh_sh = p.bhw_sh - p.bw_sh;
+      const int hq = base & ((1 << bh_sh) - 1), nq = base >> bh_sh;
+      for (int t = 0; t < ntaps; ++t) {
+        const Tap tp = p.taps[grp][t];
+        const int cw = w0 + tp.db, chh = h0 + tp.da + hq, cn = n0 + nq, cph = tp.ph;
+        int ca = tp.c_off, ckb = tp.k_off;
+        for (int cb = 0; cb < red_blocks; ++cb, ca += kKBlock, ckb += kKBlock) {
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* a = stages + s * S::kStageBytes;
+          uint8_t* b = a + kABytes;
+          mbar_expect_tx(&full[s], S::kStageBytes);
+          if (CL == 1) tma_load_5d(a, &tmA, &full[s], ca, cw, cph, chh, cn);
+          else         tma_load_5d_mc(a + q * (kTileM / CL) * 128, &tmA, &full[s], ca, cw, cph, chh, cn, kClusterMask);
+          if (!B_MN) {
+            tma_load_2d(b, &tmB, &full[s], ckb, c_out0);
+          } else {
 #pragma unroll
-          for (int j = 0; j < BLOCK_N / 64; ++j)
-            tma_load_2d(b + j * 8192, &tmB, &full[s], tp.k_off + c_out0 + j * 64, cb * kKBlock);
+            for (int j = 0; j < BLOCK_N / 64; ++j)
+              tma_load_2d(b + j * 8192, &tmB, &full[s], tp.k_off + c_out0 + j * 64, cb * kKBlock);
+          }
+          if (++s == nst) { s = 0; ph ^= 1u; }
         }
       }
     }
@@ -575,14 +584,17 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     // ===================== MMA issuer (one thread) =====================
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(kTileM, BLOCK_N, 0, B_MN ? 1 : 0);
+      const uint32_t stage0 = smem_u32(stages);
+      // descriptors of stage 0; a stage advances the 14-bit start-address field by kStageBytes / 16
+      const uint64_t adesc0 = make_smem_desc(stage0, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? make_smem_desc(stage0 + kABytes, 8192, 1024) : make_smem_desc(stage0 + kABytes, 16, 1024);
+      int s = 0;
+      uint32_t ph = 0;
       for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % nst, ph = (kb / nst) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(stages + s * S::kStageBytes);
-        const uint32_t b_addr = a_addr + kABytes;
-        const uint64_t adesc = make_smem_desc(a_addr, 16, 1024);
-        const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+        const uint64_t adesc = adesc0 + (uint64_t)((s * S::kStageBytes) >> 4);
+        const uint64_t bdesc = bdesc0 + (uint64_t)((s * S::kStageBytes) >> 4);
 #pragma unroll
         for (int k = 0; k < kKBlock / 16; ++k) {
           // advance 16 reduction elements: K-major +32 B inside the swizzle row; MN-major +16 rows of 128 B
@@ -592,6 +604,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
         }
         if (CL == 1) umma_commit(&empty[s]);            // smem slot free once these MMAs have read it
         else umma_commit_mc(&empty[s], kClusterMask);   // ... in every CTA of the cluster
+        if (++s == nst) { s = 0; ph ^= 1u; }
       }
       umma_commit(tmem_full);              // accumulator complete
     }
@@ -673,35 +686,43 @@ __global__ void __launch_bounds__(kThreads) pairconv_kernel(const __grid_constan
 
   if (warp == 0) {
     if (elect_one()) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % nst, ph = (kb / nst) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        const Tap tp = p.taps[grp][kb / p.red_blocks];
-        const int cb = kb % p.red_blocks;
-        uint8_t* a = stages + s * kPairStage;
-        uint8_t* b = a + kABytes;
-        if (rank == 0) mbar_expect_tx(&full[s], 2 * kPairStage);        // bytes of BOTH CTAs land on my barrier
-        tma_load_5d_2sm(a, &tmA, &full[s], tp.c_off + cb * kKBlock, w0 + tp.db, tp.ph, h0 + tp.da, n0);
-        if (!B_MN) tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0 + rank * 64);
-        else       tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + c_out0 + rank * 64, cb * kKBlock);
+      int s = 0;
+      uint32_t ph = 0;
+      const int ntaps = p.ntaps[grp], red_blocks = p.red_blocks;
+      for (int t = 0; t < ntaps; ++t) {                       // division-free issue loop (see tapconv_kernel)
+        const Tap tp = p.taps[grp][t];
+        const int cw = w0 + tp.db, chh = h0 + tp.da, cph = tp.ph;
+        for (int cb = 0; cb < red_blocks; ++cb) {
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* a = stages + s * kPairStage;
+          uint8_t* b = a + kABytes;
+          if (rank == 0) mbar_expect_tx(&full[s], 2 * kPairStage);        // bytes of BOTH CTAs land on my barrier
+          tma_load_5d_2sm(a, &tmA, &full[s], tp.c_off + cb * kKBlock, cw, cph, chh, n0);
+          if (!B_MN) tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + cb * kKBlock, c_out0 + rank * 64);
+          else       tma_load_2d_2sm(b, &tmB, &full[s], tp.k_off + c_out0 + rank * 64, cb * kKBlock);
+          if (++s == nst) { s = 0; ph ^= 1u; }
+        }
       }
     }
   } else if (warp == 1) {
     if (rank == 0 && elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(256, kPairN, 0, B_MN ? 1 : 0);
+      const uint32_t stage0 = smem_u32(stages);
+      const uint64_t adesc0 = make_smem_desc(stage0, 16, 1024);
+      const uint64_t bdesc0 = B_MN ? make_smem_desc(stage0 + kABytes, 8192, 1024) : make_smem_desc(stage0 + kABytes, 16, 1024);
+      int s = 0;
+      uint32_t ph = 0;
       for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % nst, ph = (kb / nst) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t a_addr = smem_u32(stages + s * kPairStage);
-        const uint32_t b_addr = a_addr + kABytes;
-        const uint64_t adesc = make_smem_desc(a_addr, 16, 1024);
-        const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
+        const uint64_t adesc = adesc0 + (uint64_t)((s * kPairStage) >> 4);
+        const uint64_t bdesc = bdesc0 + (uint64_t)((s * kPairStage) >> 4);
 #pragma unroll
         for (int k = 0; k < kKBlock / 16; ++k)
           umma_bf16_2sm(tmem_base, adesc + (uint64_t)(k * 2), bdesc + (uint64_t)(B_MN ? k * 128 : k * 2), idesc,
                         (kb | k) != 0 ? 1u : 0u);
         umma_commit_2sm(&empty[s], 3);       // stage free in both CTAs once these MMAs have read it
+        if (++s == nst) { s = 0; ph ^= 1u; }
       }
       umma_commit_2sm(tmem_full, 3);         // accumulators of both CTAs complete
     }
@@ -730,18 +751,23 @@ __global__ void __launch_bounds__(kThreads) pairconv_kernel(const __grid_constan
 // ((1+dh)*10 + (1+dw)) * 128 B with a stride-byte-offset of 10 * 128 B between 8-row groups -- one image row of the
 // 16x8 tile is one 8-row group.  (The 128-byte swizzle is a function of absolute shared-memory address bits, so
 // windows that are not 1024-byte aligned read correctly with base_offset = 0; probed in csrc/exp_halo.cu.)
-// Two 64-column TMEM accumulators let the epilogue of tile i overlap the MMAs of tile i+1.
+// Two 64-column TMEM accumulators and TWO epilogue groups of 8 warps (own staging tile, own named barrier): group g
+// drains accumulator g, so the epilogues of tiles i and i+1 are in flight together and overlap the MMAs of tile i+2.
+// The per-tile epilogue is a chain of latencies (TMEM load, staging round trip, three block barriers, global
+// loads / atomics), ~2 us per tile; one group left the tensor pipe idle two thirds of the time.
 // ------------------------------------------------------------------------------------------
 constexpr int kHaloW = 8, kHaloH = 16;
 constexpr int kHaloRowsW = kHaloW + 2;
 constexpr int kHaloBytes = (kHaloH + 2) * kHaloRowsW * 128;      // 23040
 constexpr int kHaloSlot = 23552;                                  // rounded up to 1024
-constexpr int kHaloSlots = 4;
+constexpr int kHaloSlots = 2;
 constexpr int kHaloWBytes = 9 * 8192;
-constexpr int kHaloEpiWarps = 16;
+constexpr int kHaloEpiWarps = 16;                                         // halo2conv_kernel: one group of 16
+constexpr int kHaloGroupWarps = 8;                                        // haloconv_kernel: two groups of 8
 constexpr int kHaloThreads = 64 + 32 * kHaloEpiWarps;
 constexpr int kHaloStaging = 2 * kTileM * ConvSmem<64>::kPitch + 8192;   // dz + x tiles + reduction partials
-constexpr int kHaloSmem = 1024 + kHaloWBytes + kHaloSlots * kHaloSlot + kHaloStaging + 256;
+constexpr int kHaloSmem = 1024 + kHaloWBytes + kHaloSlots * kHaloSlot + 2 * kHaloStaging + 256;
+static_assert(kHaloSmem <= 227 * 1024, "haloconv_kernel shared memory");
 
 template <bool B_MN>
 __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_constant__ CUtensorMap tmA,
@@ -752,8 +778,8 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
   uint8_t* sW = smem;
   uint8_t* sA = sW + kHaloWBytes;
   uint8_t* staging = sA + kHaloSlots * kHaloSlot;
-  uint64_t* wfull = reinterpret_cast<uint64_t*>(staging + kHaloStaging);
-  uint64_t* fullA = wfull + 1;
+  uint64_t* wfull = reinterpret_cast<uint64_t*>(staging + 2 * kHaloStaging);     // 9 barriers: one per tap
+  uint64_t* fullA = wfull + 9;
   uint64_t* emptyA = fullA + kHaloSlots;
   uint64_t* tfull = emptyA + kHaloSlots;
   uint64_t* tempty = tfull + 2;
@@ -767,9 +793,9 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
   }
   if (warp == 1) {
     if (elect_one()) {
-      mbar_init(wfull, 1);
+      for (int t = 0; t < 9; ++t) mbar_init(&wfull[t], 1);
       for (int s = 0; s < kHaloSlots; ++s) { mbar_init(&fullA[s], 1); mbar_init(&emptyA[s], 1); }
-      for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], kHaloEpiWarps); }
+      for (int a = 0; a < 2; ++a) { mbar_init(&tfull[a], 1); mbar_init(&tempty[a], kHaloGroupWarps); }
       fence_barrier_init();
     }
     __syncwarp();
@@ -785,13 +811,20 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
   const int tiles_per_img = p.tiles_w * p.tiles_h;
   if (warp == 0) {
     if (elect_one()) {
-      mbar_expect_tx(wfull, kHaloWBytes);
+      // weights: one barrier per tap, so the first MMAs start after 8 KiB instead of 72 KiB; the first halo tile is
+      // requested right after tap 0
       for (int t = 0; t < 9; ++t) {
-        if (!B_MN) tma_load_2d(sW + t * 8192, &tmB, wfull, p.taps[0][t].k_off, 0);     // [64 co rows][64 k]
-        else       tma_load_2d(sW + t * 8192, &tmB, wfull, p.taps[0][t].k_off, 0);     // [64 co(k) rows][64 ci]
+        mbar_expect_tx(&wfull[t], 8192);
+        tma_load_2d(sW + t * 8192, &tmB, &wfull[t], t * 64, 0);     // fprop: [64 co rows][64 k]; dgrad: [64 co(k) rows][64 ci]
+        if (t == 0 && (int)blockIdx.x < p.tiles_total) {
+          const int tt = blockIdx.x;
+          const int n = tt / tiles_per_img, r = tt % tiles_per_img;
+          mbar_expect_tx(&fullA[0], kHaloBytes);
+          tma_load_5d(sA, &tmA, &fullA[0], 0, (r % p.tiles_w) * kHaloW - 1, 0, (r / p.tiles_w) * kHaloH - 1, n);
+        }
       }
-      int i = 0;
-      for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+      int i = 1;
+      for (int t = blockIdx.x + gridDim.x; t < p.tiles_total; t += gridDim.x, ++i) {
         const int s = i % kHaloSlots, ph = (i / kHaloSlots) & 1;
         const int n = t / tiles_per_img, r = t % tiles_per_img;
         const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
@@ -803,21 +836,23 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(kTileM, 64, 0, B_MN ? 1 : 0);
-      mbar_wait(wfull, 0);
+      const uint32_t w_base = smem_u32(sW);
       int i = 0;
       for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
         const int s = i % kHaloSlots, ph = (i / kHaloSlots) & 1;
         const int acc = i & 1;
-        mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);          // epilogue has drained this accumulator
+        mbar_wait(&tempty[acc], ((i >> 1) & 1) ^ 1);          // epilogue group `acc` has drained this accumulator
         mbar_wait(&fullA[s], ph);
         tc_fence_after();
         const uint32_t a_base = smem_u32(sA + s * kHaloSlot);
 #pragma unroll
         for (int tp = 0; tp < 9; ++tp) {
-          const Tap tap = p.taps[0][tp];
-          const uint32_t a_addr = a_base + ((1 + tap.da) * kHaloRowsW + (1 + tap.db)) * 128;
-          const uint64_t adesc = make_smem_desc(a_addr, 16, kHaloRowsW * 128);
-          const uint32_t b_addr = smem_u32(sW + tp * 8192);
+          // tap tp = (r, s): fprop reads the window shifted by (r-1, s-1), dgrad by (1-r, 1-s) -- compile-time offsets
+          const int r3 = tp / 3, s3 = tp % 3;
+          const int wrow = B_MN ? (2 - r3) * kHaloRowsW + (2 - s3) : r3 * kHaloRowsW + s3;
+          if (i == 0) { mbar_wait(&wfull[tp], 0); tc_fence_after(); }
+          const uint64_t adesc = make_smem_desc(a_base + wrow * 128, 16, kHaloRowsW * 128);
+          const uint32_t b_addr = w_base + tp * 8192;
           const uint64_t bdesc = B_MN ? make_smem_desc(b_addr, 8192, 1024) : make_smem_desc(b_addr, 16, 1024);
 #pragma unroll
           for (int k = 0; k < 4; ++k)
@@ -829,13 +864,15 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
       }
     }
   } else {
-    int i = 0;
-    for (int t = blockIdx.x; t < p.tiles_total; t += gridDim.x, ++i) {
+    // two epilogue groups of 8 warps; group g serves accumulator g == tiles with (i & 1) == g
+    const int g = (warp - 2) / kHaloGroupWarps;
+    const uint32_t my_staging = smem_u32(staging) + g * kHaloStaging;
+    int i = g;
+    for (int t = blockIdx.x + g * gridDim.x; t < p.tiles_total; t += 2 * gridDim.x, i += 2) {
       const int n = t / tiles_per_img, r = t % tiles_per_img;
       const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
-      const int acc = i & 1;
-      conv_epilogue<64, kHaloEpiWarps>(p, 0, n, h0, w0, 0, smem_u32(staging), tmem_base + acc * 64, &tfull[acc],
-                                       (i >> 1) & 1, &tempty[acc]);
+      conv_epilogue<64, kHaloGroupWarps, 2>(p, 0, n, h0, w0, 0, my_staging, tmem_base + g * 64, &tfull[g], (i >> 1) & 1,
+                                         &tempty[g], 64 + g * 32 * kHaloGroupWarps, 1 + g);
     }
   }
 
@@ -846,7 +883,6 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
     tmem_dealloc(tmem_base, 128);
   }
 }
-
 // ------------------------------------------------------------------------------------------
 // halo2conv_kernel: the halo scheme for 3x3 stride-1 convolutions with 128 reduction channels (layer2: 16x16
 // images, 128 -> 128 channels; fprop and dgrad).  The output channels are cut into 64-wide slices (gridDim.y); a CTA
@@ -1058,45 +1094,66 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
 
   if (warp == 0) {
     if (elect_one()) {
+      // division-free issue loop: (tw, th, tn) and (stage, phase) are running counters; the taps of this group live
+      // in registers (at most 512 / NB of them)
+      int t = kb0;
+      int tw = t % p.tiles_w; t /= p.tiles_w;
+      int th = t % p.tiles_h; t /= p.tiles_h;
+      int tn = t;
+      const int tiles_w = p.tiles_w, tiles_h = p.tiles_h, BW = p.BW, BH = p.BH, BN = p.BN;
+      const int stage_bytes = p.stage_bytes, co_alias = p.co_alias;
+      int tc[S::kMaxTaps], tdb[S::kMaxTaps], tph[S::kMaxTaps], tda[S::kMaxTaps];
+#pragma unroll
+      for (int tp = 0; tp < S::kMaxTaps; ++tp) {
+        const Tap tap = p.taps[tg][tp < ntaps ? tp : 0];
+        tc[tp] = tap.c_off + cic * NB; tdb[tp] = tap.db; tph[tp] = tap.ph; tda[tp] = tap.da;
+      }
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % kWS, ph = (i / kWS) & 1;
         mbar_wait(&empty[s], ph ^ 1);
-        int t = kb0 + i;
-        const int tw = t % p.tiles_w; t /= p.tiles_w;
-        const int th = t % p.tiles_h; t /= p.tiles_h;
-        const int w0 = tw * p.BW, h0 = th * p.BH, n0 = t * p.BN;
-        uint8_t* dy = stages + (size_t)s * p.stage_bytes;
+        const int w0 = tw * BW, h0 = th * BH, n0 = tn * BN;
+        uint8_t* dy = stages + (size_t)s * stage_bytes;
         uint8_t* x = dy + S::kDyBytes;
         mbar_expect_tx(&full[s], stage_tx);
         tma_load_5d(dy, &tmDy, &full[s], cot * 128, w0, 0, h0, n0);
-        if (!p.co_alias) tma_load_5d(dy + dy_atom_bytes, &tmDy, &full[s], cot * 128 + 64, w0, 0, h0, n0);
-        for (int tp = 0; tp < ntaps; ++tp) {
-          const Tap tap = p.taps[tg][tp];
+        if (!co_alias) tma_load_5d(dy + dy_atom_bytes, &tmDy, &full[s], cot * 128 + 64, w0, 0, h0, n0);
 #pragma unroll
-          for (int j = 0; j < NB / 64; ++j)
-            tma_load_5d(x + tp * S::kXBytes + j * 8192, &tmX, &full[s], tap.c_off + cic * NB + j * 64,
-                        w0 + tap.db, tap.ph, h0 + tap.da, n0);
+        for (int tp = 0; tp < S::kMaxTaps; ++tp) {
+          if (tp < ntaps) {
+#pragma unroll
+            for (int j = 0; j < NB / 64; ++j)
+              tma_load_5d(x + tp * S::kXBytes + j * 8192, &tmX, &full[s], tc[tp] + j * 64, w0 + tdb[tp], tph[tp],
+                          h0 + tda[tp], n0);
+          }
         }
+        if (++s == kWS) { s = 0; ph ^= 1u; }
+        if (++tw == tiles_w) { tw = 0; if (++th == tiles_h) { th = 0; ++tn; } }
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(128, NB, 1, 1);       // both operands MN-major
+      const uint32_t stage0 = smem_u32(stages);
+      const uint32_t stage_bytes = (uint32_t)p.stage_bytes;
+      const uint64_t adesc0 = make_smem_desc(stage0, p.co_alias ? 0 : dy_atom_bytes, 1024);
+      const uint64_t bdesc0 = make_smem_desc(stage0 + S::kDyBytes, 8192, 1024);
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % kWS, ph = (i / kWS) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t dy_addr = smem_u32(stages + (size_t)s * p.stage_bytes);
-        const uint32_t x_addr = dy_addr + S::kDyBytes;
-        const uint64_t adesc = make_smem_desc(dy_addr, p.co_alias ? 0 : dy_atom_bytes, 1024);
+        const uint64_t soff = (uint64_t)((s * stage_bytes) >> 4);
+        const uint64_t adesc = adesc0 + soff;
         for (int tp = 0; tp < ntaps; ++tp) {
-          const uint64_t bdesc = make_smem_desc(x_addr + tp * S::kXBytes, 8192, 1024);
+          const uint64_t bdesc = bdesc0 + soff + (uint64_t)((tp * S::kXBytes) >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k)          // 64 pixels = 4 x UMMA_K(16); +16 rows of 128 B per step
             umma_bf16(tmem_base + tp * NB, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc,
                       (i | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty[s]);
+        if (++s == kWS) { s = 0; ph ^= 1u; }
       }
       umma_commit(tmem_full);
     }
@@ -1208,26 +1265,32 @@ __global__ void __launch_bounds__(kThreads) wgrad_halo_kernel(const __grid_const
 
   if (warp == 0) {
     if (elect_one()) {
+      int t = kb0;                                            // division-free issue loop (see tapconv_kernel)
+      int tw = t % p.tiles_w; t /= p.tiles_w;
+      int th = t % p.tiles_h; t /= p.tiles_h;
+      int tn = t;
+      const int tiles_w = p.tiles_w, tiles_h = p.tiles_h;
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % nst, ph = (i / nst) & 1;
         mbar_wait(&empty[s], ph ^ 1);
-        int t = kb0 + i;
-        const int tw = t % p.tiles_w; t /= p.tiles_w;
-        const int th = t % p.tiles_h; t /= p.tiles_h;
         uint8_t* dy = smem + s * kWhStage;
         mbar_expect_tx(&full[s], kWhDyBytes + kWhXBytes);
-        tma_load_5d(dy, &tmDy, &full[s], cot * 64, tw * 8, 0, th * 8, t);
-        tma_load_5d(dy + kWhDyBytes, &tmX, &full[s], cic * 64, tw * 8 - 1, 0, th * 8 - 1, t);
+        tma_load_5d(dy, &tmDy, &full[s], cot * 64, tw * 8, 0, th * 8, tn);
+        tma_load_5d(dy + kWhDyBytes, &tmX, &full[s], cic * 64, tw * 8 - 1, 0, th * 8 - 1, tn);
+        if (++s == nst) { s = 0; ph ^= 1u; }
+        if (++tw == tiles_w) { tw = 0; if (++th == tiles_h) { th = 0; ++tn; } }
       }
     }
   } else if (warp == 1) {
     if (elect_one()) {
       constexpr uint32_t idesc = make_idesc_bf16(128, 64, 1, 1);      // both operands MN-major
+      int s = 0;
+      uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
-        const int s = i % nst, ph = (i / nst) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
-        const uint32_t dy_addr = smem_u32(smem + s * kWhStage);
+        const uint32_t dy_addr = smem_u32(smem) + s * kWhStage;
         const uint32_t x_addr = dy_addr + kWhDyBytes;
         const uint64_t bdesc = make_smem_desc(dy_addr, 8192, 1024);
 #pragma unroll
@@ -1241,6 +1304,7 @@ __global__ void __launch_bounds__(kThreads) wgrad_halo_kernel(const __grid_const
                       (i | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty[s]);
+        if (++s == nst) { s = 0; ph ^= 1u; }
       }
       umma_commit(tmem_full);
     }

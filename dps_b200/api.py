@@ -38,7 +38,10 @@ class Job:
     """Bootstraps one rank: process group, symmetric arenas, parameter shard, worker engine."""
 
     def __init__(self, cfg: Config, rank: Optional[int] = None, world: Optional[int] = None,
-                 device_index: Optional[int] = None, init_state: Optional[Dict[str, torch.Tensor]] = None):
+                 device_index: Optional[int] = None, init_state: Optional[Dict[str, torch.Tensor]] = None,
+                 engine_factory=None):
+        """engine_factory: baseline harnesses only (bench_tools/torch_engine.py runs the same arenas through
+        ATen/cuDNN); the product has ONE engine, the sm_100a kernels of models/engine.py."""
         from .parallel.ps_device import DevicePS
         self.rank = _env_int("RANK", 0) if rank is None else rank
         self.world = _env_int("WORLD_SIZE", 1) if world is None else world
@@ -52,6 +55,7 @@ class Job:
                 "dps_b200.rpc.client.DistributedWorker), see INTEGRATION.md.")
         torch.cuda.set_device(self.device_index)
         self.device = torch.device("cuda", self.device_index)
+        self.engine_factory = engine_factory
         self.group = None
         if self.world > 1:
             import torch.distributed as dist
@@ -133,11 +137,14 @@ class ParameterServer:
             self.job.layout.flatten_into(flat, mom)
             shards = self.job.layout.to_shards(flat.to(self.job.device))
             self.ps.mom[self.job.rank].copy_(shards[self.job.rank])
+        # every shard has its own version counter (async mode advances them independently): restore this shard's,
+        # falling back to the job-wide step for checkpoints written with a different shard count
+        from .ops import _lib as L
         step = int(side.get("global_step", 0))
-        self.ps.flags[self.job.rank][98] = step             # DPS_F_VERSION
-        if self.cfg.mode == "async":
-            # published shard carries the restored weights already (load_master); align the version view
-            pass
+        versions = side.get("shard_versions") or []
+        mine = int(versions[self.job.rank]) if len(versions) == self.job.world else step
+        self.ps.flags[self.job.rank][L.F_VERSION] = mine
+        torch.cuda.synchronize(self.job.device)
 
     def _all_versions(self) -> List[int]:
         v = torch.tensor([self.ps.version()], device=self.job.device, dtype=torch.int64)
@@ -206,7 +213,7 @@ class Worker:
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self._ring = [torch.zeros(2, dtype=torch.float32).pin_memory() for _ in range(4)]
         self._events = [torch.cuda.Event() for _ in range(4)]
-        self.engine_kind = self.cfg.engine
+        self.engine_kind = "native" if job.engine_factory is None else "baseline"
         if self.engine_kind == "native":
             from .models.engine import ResNetEngine
             self.engine = ResNetEngine(job.layout, self.ps.wbf16[self.rank], self.ps.small[self.rank],
@@ -215,10 +222,9 @@ class Worker:
                                        device=job.device)
             self.engine.load_bn_buffers(job.model_cpu.state_dict())
         else:
-            from .models.torch_engine import TorchEngine
-            self.engine = TorchEngine(job.layout, self.ps.wbf16[self.rank], self.ps.small[self.rank],
-                                      self.ps.grad[self.rank], job.model_cpu, batch=self.cfg.batch_size,
-                                      image_size=self.cfg.image_size, device=job.device)
+            self.engine = job.engine_factory(job.layout, self.ps.wbf16[self.rank], self.ps.small[self.rank],
+                                             self.ps.grad[self.rank], job.model_cpu, batch=self.cfg.batch_size,
+                                             image_size=self.cfg.image_size, device=job.device)
         self._accum = 0
         if self.overlap_pull:
             self._side = torch.cuda.Stream(device=job.device)

@@ -8,7 +8,7 @@ test accuracy / time, draws a 2x2 summary figure and writes a summary JSON.
 B200 design: on a GPU the "local optimizer" is the one-shard parameter server of this framework (world size 1):
 the fused push kernel applies momentum + weight decay + the step in the same launch that reduces the gradient,
 the whole iteration is one CUDA-graph replay, and the learning rate lives in device memory so the schedule can
-change it between epochs without re-capturing.  Without a GPU (or with ``--engine cpu``) it runs the plain
+change it between epochs without re-capturing.  Without a GPU (or with ``--device cpu``) it runs the plain
 PyTorch loop on the CPU, which is also what the CPU test exercises.  The figure is a headless PNG (no matplotlib,
 no window): the reference's ``plt.show()`` has no counterpart.
 
@@ -175,7 +175,7 @@ def _train_device(cfg: Config, metrics: TrainingMetrics, milestones, gamma, log,
             if max_steps is not None and steps >= max_steps:
                 break
         n_params = sum(e.numel for e in job.layout.entries.values())
-        return n_params, f"cuda ({torch.cuda.get_device_name(0)}, engine={cfg.engine})"
+        return n_params, f"cuda ({torch.cuda.get_device_name(0)}, sm_100a kernels)"
     finally:
         job.close()
 
@@ -218,7 +218,6 @@ def main(argv=None) -> int:
     p.add_argument("--train-samples", type=int, default=50000)
     p.add_argument("--test-samples", type=int, default=10000)
     p.add_argument("--device", choices=["auto", "cpu", "cuda"], default="auto")
-    p.add_argument("--engine", choices=["native", "torch"], default="native")
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--max-steps", type=int, default=None)
     p.add_argument("--eval-batches", type=int, default=None)
@@ -226,7 +225,7 @@ def main(argv=None) -> int:
     a = p.parse_args(argv)
     cfg = Config(workers=1, epochs=a.epochs, batch_size=a.batch_size, lr=a.lr, momentum=a.momentum,
                  weight_decay=a.weight_decay, dataset=a.dataset, data_root=a.data_root,
-                 train_samples=a.train_samples, test_samples=a.test_samples, device=a.device, engine=a.engine,
+                 train_samples=a.train_samples, test_samples=a.test_samples, device=a.device,
                  seed=a.seed).validate()
     ms = [int(t) for t in a.milestones.split(",") if t]
     run(cfg, ms, a.gamma, a.output_dir, max_steps=a.max_steps, eval_batches=a.eval_batches)

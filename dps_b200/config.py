@@ -67,7 +67,7 @@ class Config:
     data_on_device: bool = True           # GPU path: dataset resident in HBM, augmentation kernel per batch
     # ---- device path -------------------------------------------------------
     device: str = "auto"                  # 'auto' | 'cpu' | 'cuda'
-    engine: str = "native"                # 'native' (sm_100a kernels) | 'torch' (ATen/cuDNN)
+    engine: str = "native"                # the sm_100a kernels; the ATen/cuDNN baseline lives in bench_tools/torch_engine.py
     use_cuda_graph: bool = True
     overlap_pull: bool = True             # sync mode: pull at step start, overlapped with forward per layer group
     async_ring_slots: int = 4             # ring depth per (owner, worker) pair
@@ -139,7 +139,6 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--data-on-host", dest="data_on_device", action="store_false",
                    help="GPU path: produce batches on the host (loader thread + pinned H2D) instead of on the device")
     p.add_argument("--device", choices=["auto", "cpu", "cuda"], default="auto")
-    p.add_argument("--engine", choices=["native", "torch"], default="native")
     p.add_argument("--bn-buffer-policy", choices=["reference", "local", "mean"], default="mean")
     p.add_argument("--local-step-policy", choices=["reference", "accumulate"], default="accumulate")
     p.add_argument("--nonblocking-sync", action="store_true")

@@ -192,8 +192,8 @@ class ResNetEngine:
         self.units, self.blocks = units, blocks
         self.feat, self.featH, self.F = x, H, Cin
 
-        # per-step zeroed scratch: [fwd stats | bwd sums] for every BN (fp64: order-independent atomics)
-        self.scratch = torch.zeros(self._scratch_need, dtype=torch.float64, device=dev)
+        # per-step zeroed scratch: [fwd stats | bwd sums] for every BN (64-bit fixed point: order-independent atomics)
+        self.scratch = torch.zeros(self._scratch_need, dtype=torch.int64, device=dev)
         for bn, (off, Cc) in zip(self.bns, self._scratch_slices):
             bn.stats = self.scratch[off: off + 2 * Cc]
             bn.bsums = self.scratch[off + 2 * Cc: off + 4 * Cc]

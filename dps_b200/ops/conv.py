@@ -47,6 +47,7 @@ class ConvPlan:
         bn, sm = C.c_int(), C.c_int()
         L.check(L.lib().dps_conv_plan_info(C.c_void_p(handle), C.byref(info), C.byref(bn), C.byref(sm)), "plan_info")
         self.grid, self.block_n, self.smem = tuple(info), bn.value, sm.value
+        self.desc = ""                      # human-readable shape, set by the factories (timeline / profiles)
 
     @classmethod
     def fprop(cls, x, w, out, *, N, H, W, Cin, Cout, R, stride, stats=None, w_cols=None, w_pitch=None):
@@ -56,7 +57,9 @@ class ConvPlan:
         w_pitch = R * R * Cin if w_pitch is None else w_pitch
         L.check(L.lib().dps_conv_plan_create(0, _ptr(x), _ptr(w), _ptr(out), None, _ptr(stats), N, H, W, Cin, Cout,
                                              R, stride, w_cols, w_pitch, C.byref(h)), "conv_plan_create(fprop)")
-        return cls(h.value, cls.FPROP, (x, w, out, stats))
+        pl = cls(h.value, cls.FPROP, (x, w, out, stats))
+        pl.desc = f"H{H} {Cin}->{Cout} k{R} s{stride}"
+        return pl
 
     @classmethod
     def dgrad(cls, dy, w, dx, *, N, H, W, Cin, Cout, R, stride, addend=None, w_cols=None, w_pitch=None):
@@ -67,7 +70,9 @@ class ConvPlan:
         w_pitch = R * R * Cin if w_pitch is None else w_pitch
         L.check(L.lib().dps_conv_plan_create(1, _ptr(dy), _ptr(w), _ptr(dx), _ptr(addend), None, N, H, W, Cin, Cout,
                                              R, stride, w_cols, w_pitch, C.byref(h)), "conv_plan_create(dgrad)")
-        return cls(h.value, cls.DGRAD, (dy, w, dx, addend))
+        pl = cls(h.value, cls.DGRAD, (dy, w, dx, addend))
+        pl.desc = f"H{H} {Cin}->{Cout} k{R} s{stride}"
+        return pl
 
     @classmethod
     def wgrad(cls, x, dy, dw, *, N, H, W, Cin, Cout, R, stride, valid_cols=None, dw_pitch=None, nsplit=0):
@@ -77,7 +82,9 @@ class ConvPlan:
         dw_pitch = R * R * Cin if dw_pitch is None else dw_pitch
         L.check(L.lib().dps_wgrad_plan_create(_ptr(x), _ptr(dy), _ptr(dw), N, H, W, Cin, Cout, R, stride, valid_cols,
                                               dw_pitch, nsplit, C.byref(h)), "wgrad_plan_create")
-        return cls(h.value, cls.WGRAD, (x, dy, dw))
+        pl = cls(h.value, cls.WGRAD, (x, dy, dw))
+        pl.desc = f"H{H} {Cin}->{Cout} k{R} s{stride}"
+        return pl
 
     def fuse_bn_bwd(self, y, x, mean, rstd, sums) -> "ConvPlan":
         """dgrad only: the epilogue also does the next BatchNorm's backward reduction (dz = dy*(y>0), sums)."""

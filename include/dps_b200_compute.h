@@ -80,14 +80,6 @@ int dps_augment_batch(const unsigned char* src, const long long* src_labels, con
                       unsigned long long counter0, int train, int pad, const float* mean3, const float* std3,
                       void* stream);
 
-/* ---- hardware probe (no counterpart in the reference; used by bench_tools/exp_halo.py, not by the framework):
- *      one 128-pixel x 64-channel 3x3 output tile computed from ONE halo tile with shifted-window UMMA descriptors.
- *      variant 0: descriptor base_offset field = 0; variant 1: base_offset = (start_address >> 7) & 7.  out is
- *      [128][64] fp32.  Variant 0 is the correct one: the 128-byte swizzle is a function of absolute shared-memory
- *      address bits, so a window may start at any 128-byte row of a TMA-written tile. ---- */
-int dps_exp_halo_tile(const void* x, const void* w, float* out, int N, int H, int W, int n, int h0, int w0, int variant,
-                      void* stream);
-
 #ifdef __cplusplus
 }
 #endif
