@@ -184,7 +184,8 @@ def run_ours(args) -> dict:
 
     err = job.ps.error_bits()
     value = K * B * world / (ms_dev / 1e3)
-    ps_launches = (8 if wk.overlap_pull else 3) if cfg.mode == "sync" else 4
+    # data-path launches per step, counted while the step graph was captured (eager path: the documented counts)
+    ps_launches = getattr(wk, "ps_launches_per_step", None) or ((8 if wk.overlap_pull else 3) if cfg.mode == "sync" else 4)
     kernels = getattr(wk.engine, "kernels_per_step", 0)
     out = {
         "metric": "ResNet-18 images/sec (%s mode, parameter server)" % cfg.mode,

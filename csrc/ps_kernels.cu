@@ -78,21 +78,34 @@ __device__ __forceinline__ bool wait_ge(const uint32_t* flag, uint32_t target, u
 // PUSH (sync): scatter fp16 gradient tiles to owners, barrier on per-source arrival counters,
 // W-way mean + SGD(momentum, weight decay) on the owner's fp32 master shard.
 // grid = G CTAs (G <= resident CTAs: owner-side CTAs spin, so the whole grid must be co-resident).
+//
+// The kernel works on the LOCAL shard range [seg_lo, seg_hi) and runs the phases selected by `phases`:
+//   bit 0 (SEND)   : compress + peer stores + arrival signal.  Never waits, so it can be launched per layer group
+//                    from the backward pass as soon as that group's weight gradients are complete (the arena is in
+//                    forward order; layer groups are contiguous ranges of every shard).
+//   bit 1 (REDUCE) : wait until every live source has signalled `arrivals_per_step` times this round, then mean + SGD.
+// One launch with phases = 3 over [0, E) is the monolithic push; the overlapped step sends fc / layer4 / layer3 /
+// layer2 on a side stream during backward and ends with SEND(first group) + REDUCE(everything).
+// Membership: DPS_F_ALIVE is this owner's mask of sources it still waits for.  A source that misses a barrier
+// (timeout) is dropped from the mask for good -- later rounds neither wait for it nor read its stale staging slot --
+// and the sticky error bit tells the host watchdog to checkpoint and restart the job.
 // ------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ DpsTables T, uint32_t step_arg,
                                                         float lr_arg, float momentum, float weight_decay,
-                                                        int compress_fp16, unsigned long long timeout_ns) {
+                                                        int compress_fp16, unsigned long long timeout_ns,
+                                                        long long seg_lo, long long seg_hi, int phases,
+                                                        uint32_t arrivals_per_step) {
   const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
   const float lr = T.lr_ptr ? *T.lr_ptr : lr_arg;
   const int W = T.world, BS = T.block_elems;
   const long long E = T.shard_elems;
   const int G = gridDim.x, b = blockIdx.x;
-  const long long per = ((E / VEC + G - 1) / G) * VEC;       // elements per CTA per shard
-  const long long lo = (long long)b * per, hi = min(E, lo + per);
+  const long long per = (((seg_hi - seg_lo) / VEC + G - 1) / G) * VEC;       // elements per CTA per shard
+  const long long lo = seg_lo + (long long)b * per, hi = min(seg_hi, lo + per);
   __shared__ uint32_t s_present;
 
   // ---- phase A: every rank handled by this launch sends its slice of every shard to that shard's owner
-  for (int r = T.rank_lo; r < T.rank_hi; ++r) {
+  for (int r = T.rank_lo; r < T.rank_hi && (phases & 1); ++r) {
     float* grad = T.grad[r];
     for (int oo = 0; oo < W; ++oo) {
       const int o = (r + 1 + oo) % W;                        // rotate so owners are hit evenly
@@ -124,18 +137,26 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     __syncthreads();
   }
 
-  // ---- phase B: owners wait for all sources, reduce and update
-  const uint32_t target = (step + 1) * (uint32_t)G;
+  // ---- phase B: owners wait for all live sources, reduce and update
+  if (!(phases & 2)) return;
+  const uint32_t target = (step + 1) * arrivals_per_step;
   for (int o = T.rank_lo; o < T.rank_hi; ++o) {
-    if (threadIdx.x == 0) {
-      uint32_t present = 0;
-      for (int s = 0; s < W; ++s)
-        if (wait_ge(T.flags[o] + DPS_F_ARRIVE + s, target, timeout_ns)) present |= 1u << s;
-      if (present != (W >= 32 ? 0xffffffffu : ((1u << W) - 1u))) {
-        atomicOr(T.flags[o] + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
-        T.flags[o][DPS_F_MISSING] = ~present;
+    if (threadIdx.x < 32) {
+      // warp-parallel poll: lane s watches source s (W <= 32), so a round costs ONE flag latency and a missing
+      // source costs ONE timeout, not W of them in sequence
+      const int s = threadIdx.x;
+      const uint32_t alive = T.flags[o][DPS_F_ALIVE];
+      bool ok = false;
+      if (s < W && ((alive >> s) & 1u)) ok = wait_ge(T.flags[o] + DPS_F_ARRIVE + s, target, timeout_ns);
+      const uint32_t present = __ballot_sync(0xffffffffu, ok);
+      if (s == 0) {
+        if (present != alive) {                                // somebody we still counted on did not arrive
+          atomicOr(T.flags[o] + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
+          atomicOr(T.flags[o] + DPS_F_MISSING, alive & ~present);
+          atomicAnd(T.flags[o] + DPS_F_ALIVE, present);
+        }
+        s_present = present;
       }
-      s_present = present;
     }
     __syncthreads();
     const uint32_t present = s_present;
@@ -249,13 +270,17 @@ __global__ void __launch_bounds__(256) pull_seg_kernel(const __grid_constant__ D
   }
 }
 
+// Deliveries expected so far are ACCUMULATED on the device (DPS_F_SEGEXPECT / DPS_F_PULLEXPECT += live owners x CTAs
+// per round) instead of being derived from the round number, so owners dropped from DPS_F_ALIVE stop being waited for.
 __global__ void wait_seg_kernel(const __grid_constant__ DpsTables T, int rank, int seg, uint32_t step_arg,
                                 uint32_t ctas_per_owner, unsigned long long timeout_ns) {
   if (threadIdx.x == 0) {
-    const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
-    const uint32_t target = (step + 1) * ctas_per_owner * (uint32_t)T.world;
-    if (!wait_ge(T.flags[rank] + DPS_F_SEGCOUNT + seg, target, timeout_ns))
-      atomicOr(T.flags[rank] + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
+    (void)step_arg;
+    uint32_t* f = T.flags[rank];
+    const uint32_t live = (uint32_t)__popc(f[DPS_F_ALIVE]);
+    const uint32_t target = f[DPS_F_SEGEXPECT + seg] + ctas_per_owner * live;
+    f[DPS_F_SEGEXPECT + seg] = target;
+    if (!wait_ge(f + DPS_F_SEGCOUNT + seg, target, timeout_ns)) atomicOr(f + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
   }
 }
 
@@ -269,9 +294,10 @@ __global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, 
                                  uint32_t ctas_per_owner, unsigned long long timeout_ns, int bump) {
   if (threadIdx.x == 0) {
     const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
-    const uint32_t target = (step + 1) * ctas_per_owner * (uint32_t)T.world;
-    if (!wait_ge(T.flags[rank] + DPS_F_PULLCOUNT, target, timeout_ns))
-      atomicOr(T.flags[rank] + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
+    uint32_t* f = T.flags[rank];
+    const uint32_t target = f[DPS_F_PULLEXPECT] + ctas_per_owner * (uint32_t)__popc(f[DPS_F_ALIVE]);
+    f[DPS_F_PULLEXPECT] = target;
+    if (!wait_ge(f + DPS_F_PULLCOUNT, target, timeout_ns)) atomicOr(f + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
     if (bump && T.step_ctr) T.step_ctr[0] = step + 1;     // last kernel of the round: safe to advance
   }
 }
@@ -516,7 +542,21 @@ DPS_API int dps_push_sync(const DpsTables* T, unsigned step, float lr, float mom
                           int compress_fp16, int ctas, unsigned long long timeout_ns, void* stream) {
   if (int e = check_tables(T)) return e;
   push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
-                                                          timeout_ns);
+                                                          timeout_ns, 0, T->shard_elems, 3, (uint32_t)ctas);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+DPS_API int dps_push_segment(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
+                             int compress_fp16, int ctas, unsigned long long timeout_ns, long long seg_lo,
+                             long long seg_hi, int phases, unsigned arrivals_per_step, void* stream) {
+  if (int e = check_tables(T)) return e;
+  if (seg_lo < 0 || seg_hi > T->shard_elems || seg_lo > seg_hi || seg_lo % 8 || seg_hi % 8)
+    DPS_FAIL(1, "push_segment: bad range [%lld, %lld)", seg_lo, seg_hi);
+  if (!(phases & 3)) DPS_FAIL(1, "push_segment: phases must select SEND (1) and/or REDUCE (2)");
+  if (ctas < 1) DPS_FAIL(1, "push_segment: ctas must be positive");
+  push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
+                                                          timeout_ns, seg_lo, seg_hi, phases, arrivals_per_step);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

@@ -231,6 +231,15 @@ class Worker:
             self.ps.set_segments(self.engine.segment_boundaries)
             self.engine.seg_wait = lambda k: self.ps.wait_segment(k)
             self._weights_stale = False
+        if self.overlap_push:
+            # weight gradients and the per-group SEND half of the push run on a second stream beside the
+            # dgrad / BatchNorm chain of the backward pass; only the first layer group + the reduce stay exposed
+            self._wstream = torch.cuda.Stream(device=job.device)
+            self.engine.side_stream = self._wstream
+            self.engine.on_group_done = self._send_group
+            nseg = self.ps.nseg
+            self._send_ctas = [self.ps.send_ctas(k) for k in range(nseg)]
+            self._arrivals = sum(self._send_ctas)
 
     # ------------------------------------------------------------------ the step
     @property
@@ -240,6 +249,18 @@ class Worker:
         next forward pass)."""
         return (self.cfg.overlap_pull and self.cfg.mode == "sync" and self.engine_kind == "native"
                 and self.cfg.sync_steps == 1)
+
+    @property
+    def overlap_push(self) -> bool:
+        """Sync mode with the overlapped pull: the push is also split per layer group and sent while the backward
+        pass is still running (the reference pushes once, after the whole backward: worker.py:376)."""
+        return self.overlap_pull and self.cfg.overlap_push
+
+    def _send_group(self, k: int) -> None:
+        """Called by the engine on the weight-gradient stream when every gradient of layer group k is complete."""
+        if k == 0:
+            return                                       # first group: sent on the main stream with the reduce
+        self.ps.push_segment(k, self.ps.SEND, ctas=self._send_ctas[k])
 
     def _pre(self) -> None:
         """Start of a step: fork the segmented pull onto the side stream."""
@@ -252,7 +273,14 @@ class Worker:
 
     def _exchange(self) -> None:
         """Everything after backward: push -> (barrier, reduce, SGD | ring, staleness apply) -> pull."""
-        if self.overlap_pull:
+        if self.overlap_push:
+            # groups 1.. were sent during backward (engine.on_group_done); BN affine gradients, the stem and layer1
+            # finish last: send them now, then reduce the whole shard once every source has signalled all its groups
+            self.ps.push_segment(0, self.ps.SEND, ctas=self._send_ctas[0])
+            self.ps.push_segment(-1, self.ps.REDUCE, arrivals_per_step=self._arrivals)
+            self.ps.bump_step()
+            torch.cuda.current_stream().wait_stream(self._side)      # join the pull branch
+        elif self.overlap_pull:
             self.ps.push_sync()
             self.ps.bump_step()
             torch.cuda.current_stream().wait_stream(self._side)      # join the pull branch
@@ -271,9 +299,11 @@ class Worker:
         fused = self.cfg.sync_steps == 1
         # one graph per staging slot: graph k reads the batch straight from slot k and ends with the D2H copy of
         # (loss, #correct) into pinned slot k -- no eager copies between two replays
+        before = self.ps.launches
         self.engine.capture(extra=self._exchange if fused else None, pre=self._pre,
                             inputs=list(zip(self._stage_x, self._stage_y)),
                             post=lambda k: self._ring[k].copy_(self.engine.out, non_blocking=True))
+        self.ps_launches_per_step = (self.ps.launches - before) // max(1, len(self.engine.graphs))
         for k, v in self.engine.bn_buffers().items():
             v.copy_(saved[k])
         # capture ran one eager warm-up step on the engine only: clear what it accumulated
@@ -401,8 +431,7 @@ class Worker:
             ev[2].record()
             with _R("backward"):
                 if native:
-                    for f in self.engine.bwd:
-                        f()
+                    self.engine.backward()
                 else:
                     self.engine.forward_backward()       # autograd: forward and backward are one call
             ev[3].record()

@@ -70,6 +70,7 @@ class Config:
     engine: str = "native"                # the sm_100a kernels; the ATen/cuDNN baseline lives in bench_tools/torch_engine.py
     use_cuda_graph: bool = True
     overlap_pull: bool = True             # sync mode: pull at step start, overlapped with forward per layer group
+    overlap_push: bool = True             # sync mode: weight gradients + per-group push on a side stream during backward
     async_ring_slots: int = 4             # ring depth per (owner, worker) pair
     # ---- outputs -----------------------------------------------------------
     metrics_dir: Optional[str] = None     # write METRICS_JSON records to files here

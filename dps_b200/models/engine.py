@@ -41,6 +41,17 @@ def _p(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
+class _GroupDone:
+    """Marker in the backward schedule: every weight gradient of layer group `k` has been issued."""
+
+    def __init__(self, engine: "ResNetEngine", k: int):
+        self.engine, self.k = engine, k
+
+    def __call__(self) -> None:
+        if self.engine.on_group_done is not None:
+            self.engine.on_group_done(self.k)
+
+
 @dataclass
 class _BN:
     name: str                 # state_dict prefix, e.g. 'layer1.0.bn1'
@@ -81,6 +92,10 @@ class ResNetEngine:
         self._build()
         self.graph: Optional[torch.cuda.CUDAGraph] = None
         self.seg_wait: Optional[Callable[[int], None]] = None   # set by the worker: wait for a pulled layer group
+        # set by the worker: weight gradients (which nothing in the backward chain consumes) run on `side_stream`,
+        # and `on_group_done(k)` is called there once every weight gradient of layer group k has been issued
+        self.side_stream: Optional[torch.cuda.Stream] = None
+        self.on_group_done: Optional[Callable[[int], None]] = None
 
     # ------------------------------------------------------------------ helpers
     def _bf(self, *shape) -> torch.Tensor:
@@ -256,6 +271,9 @@ class ResNetEngine:
             b = unit["bn"]
             return plan.fuse_bn_bwd(unit["a"], unit["c"], b.mean, b.rstd, b.bsums)
 
+        self._side_plans = set()                 # weight-gradient plans: leaves of the backward graph
+        nseg = len(self.segment_boundaries) - 1
+        self.bwd.append(_GroupDone(self, nseg - 1))             # fc gradients come from the head kernel
         g_out, g_out_fused = self.d_feat, False
         for bi in range(len(blocks) - 1, -1, -1):
             blk = blocks[bi]
@@ -275,10 +293,12 @@ class ResNetEngine:
             p_w2 = ConvPlan.wgrad(u1["a"], g_c2, self._g(u2["wname"]), **kw2)
             p_d2 = fuse(ConvPlan.dgrad(g_c2, self._w(u2["wname"]), g_a1, **kw2), u1)
             self.bwd += [p_w2.run, p_d2.run]
+            self._side_plans |= {id(p_w2)}
             bn_apply(u1["bn"], g_a1, u1["c"], g_c1)
             kw1 = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=3, stride=stride)
             p_w1 = ConvPlan.wgrad(blk["x"], g_c1, self._g(u1["wname"]), **kw1)
             self.bwd.append(p_w1.run)
+            self._side_plans |= {id(p_w1)}
             self._keep += [p_w2, p_d2, p_w1]
             if us is None:
                 p_d1 = fuse(ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=dz2, **kw1), prev_unit)
@@ -297,15 +317,20 @@ class ResNetEngine:
                 p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=g_s, **kw1).addend_compact(True)
                 fuse(p_d1, prev_unit)
                 self.bwd += [p_ws.run, p_ds.run, p_d1.run]
+                self._side_plans |= {id(p_ws)}
                 self._keep += [p_ws, p_ds, p_d1]
             g_out, g_out_fused = g_x, True
+            if bi > 0 and bi % BLOCKS_PER_STAGE == 0:            # first block of layer (bi/2 + 1): group complete
+                self.bwd.append(_GroupDone(self, bi // BLOCKS_PER_STAGE))
         # stem
         g_c0 = self._bf(N, S, S, STAGE_WIDTHS[0])
         bn_apply(stem["bn"], g_out, stem["c"], g_c0)
         p_w0 = ConvPlan.wgrad(self.col.view(N, S, S, 64), g_c0, self._g("conv1.weight"), N=N, H=S, W=S, Cin=64,
                               Cout=STAGE_WIDTHS[0], R=1, stride=1, valid_cols=STEM_PITCH, dw_pitch=STEM_PITCH)
         self.bwd.append(p_w0.run)
+        self._side_plans |= {id(p_w0)}
         self._keep.append(p_w0)
+        self.bwd.append(_GroupDone(self, 0))
         # launches per step (bn_backward and head are two kernels each)
         self.kernels_per_step = self._count_kernels()
 
@@ -314,7 +339,7 @@ class ResNetEngine:
         n_conv = len(self.units)
         fwd = 1 + 1 + n_conv + n_bn + 2                      # memset, im2col, convs, bn, head(2)
         n_dgrad = n_conv - 1
-        bwd = 2 * self.n_bn_full + self.n_bn_apply + n_conv + n_dgrad
+        bwd = 2 * self.n_bn_full + self.n_bn_apply + n_conv + n_dgrad     # (group markers launch nothing themselves)
         return fwd + bwd
 
     # ------------------------------------------------------------------ execution
@@ -322,11 +347,32 @@ class ResNetEngine:
         self.images.copy_(images, non_blocking=True)
         self.labels.copy_(labels, non_blocking=True)
 
+    def _on_side(self, f) -> bool:
+        return isinstance(f, _GroupDone) or id(getattr(f, "__self__", None)) in self._side_plans
+
+    def backward(self) -> None:
+        """Backward schedule.  With a side stream, weight gradients (and the per-group push hooks) are forked onto it
+        right after the kernel that produced their input and joined at the end: nothing in the dgrad / BatchNorm
+        chain depends on them, so they fill the bubbles between the kernels of that chain."""
+        W = self.side_stream
+        if W is None:
+            for f in self.bwd:
+                f()
+            return
+        cur = torch.cuda.current_stream()
+        for f in self.bwd:
+            if self._on_side(f):
+                W.wait_stream(cur)
+                with torch.cuda.stream(W):
+                    f()
+            else:
+                f()
+        cur.wait_stream(W)
+
     def forward_backward(self) -> None:
         for f in self.fwd:
             f()
-        for f in self.bwd:
-            f()
+        self.backward()
 
     def forward_eval(self) -> None:
         for f in self.evalf:

@@ -21,11 +21,11 @@ HIST_BINS = 16
 FLAG_WORDS = 1024
 
 # flag-block word offsets (mirror include/dps_b200.h)
-F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS, F_DROPPED = 0, 32, 33, 34, 35, 36
+F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS, F_DROPPED, F_ALIVE, F_PULLEXPECT = 0, 32, 33, 34, 35, 36, 37, 38
 F_HEARTBEAT, F_RING_TAIL, F_RING_HEAD, F_VERSION, F_PUBSEQ, F_APPLY_DONE = 64, 96, 97, 98, 99, 100
 F_SLOTS = 128
 F_STAT_ACCEPTED, F_STAT_REJECTED, F_STAT_SUM, F_STAT_MAX, F_STAT_HIST, F_STAT_LAST = 512, 513, 514, 515, 520, 544
-F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT = 640, 704, 800, 864
+F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT, F_SEGEXPECT = 640, 704, 800, 864, 880
 ERR_BARRIER_TIMEOUT, ERR_PULL_TIMEOUT, ERR_RING_FULL = 1, 2, 4
 
 _P = C.c_void_p
@@ -65,6 +65,7 @@ def _declare(lib: C.CDLL) -> None:
         "dps_ipc_close": (i32, [_P]),
         "dps_enable_peer": (i32, [i32, i32]),
         "dps_push_sync": (i32, [TP, u32, f32, f32, f32, i32, i32, u64, _P]),
+        "dps_push_segment": (i32, [TP, u32, f32, f32, f32, i32, i32, u64, C.c_longlong, C.c_longlong, i32, u32, _P]),
         "dps_pull_bcast": (i32, [TP, u32, i32, _P]),
         "dps_wait_pull": (i32, [TP, i32, u32, i32, u64, i32, _P]),
         "dps_pull_segments": (i32, [TP, C.POINTER(C.c_longlong), i32, i32, _P]),

@@ -71,6 +71,8 @@ class DevicePS:
         self.wbf16 = {r: self.fabric.tensor(r, "wbf16", torch.bfloat16) for r in self.local}
         self.small = {r: self.fabric.tensor(r, "small", torch.float32) for r in self.local}
         self.flags = {r: self.fabric.tensor(r, "flags", torch.int32) for r in self.local}
+        for r in self.local:                 # membership: every source is waited for until it misses a barrier
+            self.flags[r][L.F_ALIVE] = (1 << world) - 1 if world < 32 else -1
 
         t = L.DpsTables()
         t.world, t.block_elems, t.ring_slots = world, layout.block_elems, self.R
@@ -156,6 +158,31 @@ class DevicePS:
                                        cfg.weight_decay, int(self.compress), self.ctas, self.timeout_ns,
                                        L.stream_ptr(stream)), "push_sync")
         self.launches += 1
+
+    # ---- segmented push (overlaps the backward pass) --------------------------------------
+    SEND, REDUCE = 1, 2
+
+    def push_segment(self, seg: int, phases: int, arrivals_per_step: Optional[int] = None, stream=None,
+                     ctas: Optional[int] = None) -> None:
+        """Push kernel on layer group `seg` of every shard (set_segments() defines the groups; seg < 0 = the whole
+        shard).  phases: SEND (never waits; launched as soon as the group's weight gradients are complete), REDUCE
+        (waits for `arrivals_per_step` signals per live source, then mean + SGD), or both."""
+        cfg = self.cfg
+        lo, hi = (0, self.E) if seg < 0 else (int(self._seg[seg]), int(self._seg[seg + 1]))
+        n = self.ctas if ctas is None else ctas
+        if lo == hi and not (phases & self.REDUCE):
+            n = 1                                     # empty group on this world size: still signal the arrival
+        L.check(self.lib.dps_push_segment(self._tp, self.step, cfg.lr, cfg.momentum, cfg.weight_decay,
+                                          int(self.compress), n, self.timeout_ns, lo, hi, phases,
+                                          arrivals_per_step if arrivals_per_step is not None else n,
+                                          L.stream_ptr(stream)), "push_segment")
+        self.launches += 1
+
+    def send_ctas(self, seg: int) -> int:
+        """CTAs of the SEND launch of a layer group: sized by the group, small enough to share the SMs with the
+        backward kernels it runs beside."""
+        n = int(self._seg[seg + 1]) - int(self._seg[seg])
+        return int(max(1, min(148, n // (256 * 8 * 4))))
 
     def pull(self, stream=None, wait: bool = True) -> None:
         L.check(self.lib.dps_pull_bcast(self._tp, self.step, self.ctas, L.stream_ptr(stream)), "pull_bcast")

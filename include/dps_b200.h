@@ -28,6 +28,8 @@ extern "C" {
 #define DPS_F_MISSING 34        /* mask of ranks missing at the last timed-out barrier           */
 #define DPS_F_TORN_PULLS 35     /* async pulls that stayed inconsistent after retries            */
 #define DPS_F_DROPPED 36        /* async pushes skipped because the owner's ring had no room     */
+#define DPS_F_ALIVE 37          /* sync: mask of source ranks this owner still waits for (set to all W at start) */
+#define DPS_F_PULLEXPECT 38     /* pull deliveries expected so far (accumulated per round: live owners x CTAs)   */
 #define DPS_F_HEARTBEAT 64      /* [32] last step seen from each source rank                     */
 #define DPS_F_RING_TAIL 96      /* async ring: next ticket (peer atomics)                        */
 #define DPS_F_RING_HEAD 97      /* async ring: tickets consumed                                  */
@@ -46,6 +48,7 @@ extern "C" {
 #define DPS_F_SEEN 800          /* [32] version of each shard at this worker's last pull         */
 #define DPS_F_DROP 832          /* [32] local: this step's push to owner o was skipped            */
 #define DPS_F_SEGCOUNT 864      /* [16] segmented pull: deliveries received per layer group           */
+#define DPS_F_SEGEXPECT 880     /* [16] segmented pull: deliveries expected so far per layer group    */
 #define DPS_MAX_SEGS 16
 #define DPS_FLAG_WORDS 1024
 
@@ -98,6 +101,12 @@ int dps_enable_peer(int device, int peer);                                  /* 0
 /* reference: worker.py:264-301 + server.py:232-288,126-169 (compress, push, decompress, mean, SGD) */
 int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
                   int compress_fp16, int ctas, unsigned long long timeout_ns, void* stream);
+/* The same kernel on the LOCAL shard range [seg_lo, seg_hi) (multiples of 8), phases: 1 = SEND only (never waits:
+ * launched per layer group during backward), 2 = REDUCE only (waits for arrivals_per_step signals per live source
+ * and round, then mean + SGD), 3 = both.  reference: the push happens once, after the whole backward (worker.py:376). */
+int dps_push_segment(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
+                     int compress_fp16, int ctas, unsigned long long timeout_ns, long long seg_lo, long long seg_hi,
+                     int phases, unsigned arrivals_per_step, void* stream);
 /* reference: server.py:213-230 + worker.py:233-262 (FetchParameters + load_state_dict) */
 int dps_pull_bcast(const DpsTables* T, unsigned step, int ctas, void* stream);
 int dps_wait_pull(const DpsTables* T, int rank, unsigned step, int ctas_per_owner, unsigned long long timeout_ns,

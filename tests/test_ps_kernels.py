@@ -286,3 +286,81 @@ def test_segmented_pull_delivers_layer_groups_in_order():
         assert counts == [W * ps.ctas] * 5
     assert ps.error_bits(0) == 0
     ps.close()
+
+
+@pytest.mark.parametrize("W,momentum", [(1, 0.0), (4, 0.9), (8, 0.0)])
+def test_segmented_push_equals_monolithic_push(W, momentum):
+    """Push overlapped with backward: SEND per layer group (last group first, each with its own CTA count), then one
+    REDUCE over the whole shard -- same master, same zeroed gradients as the single launch."""
+    model, layout, ps, flat0 = _setup(W, mode="sync", lr=0.1, momentum=momentum)
+    bounds = [0] + [layout.entries[n].offset for n in ("layer2.0.conv1.weight", "layer3.0.conv1.weight",
+                                                        "layer4.0.conv1.weight", "fc.weight")] + [layout.total]
+    ps.set_segments(bounds)
+    p, m = flat0.clone(), torch.zeros_like(flat0)
+    for step in range(3):
+        gs = [torch.randn(layout.total, device="cuda", generator=torch.Generator("cuda").manual_seed(10 * step + r)) * 0.05
+              for r in range(W)]
+        for r in range(W):
+            ps.grad[r].copy_(gs[r])
+        ctas = [ps.send_ctas(k) for k in range(ps.nseg)]
+        for k in range(ps.nseg - 1, -1, -1):
+            ps.push_segment(k, ps.SEND, ctas=ctas[k])
+        ps.push_segment(-1, ps.REDUCE, arrivals_per_step=sum(ctas))
+        ps.pull()
+        ps.step += 1
+        torch.cuda.synchronize()
+        g = torch.stack([x.half().float() for x in gs]).sum(0) / W
+        if momentum:
+            m = momentum * m + g
+            g = m
+        p = p - 0.1 * g
+        got = ps.gather_master()
+        assert torch.allclose(got, p, rtol=1e-5, atol=1e-6), float((got - p).abs().max())
+        for r in range(W):
+            assert float(ps.grad[r].abs().max()) == 0.0
+            assert torch.equal(ps.wbf16[r], got.to(torch.bfloat16))
+    assert ps.error_bits(0) == 0 and all(ps.version(r) == 3 for r in range(W))
+    ps.close()
+
+
+def test_missed_barrier_removes_the_source_from_the_membership_mask():
+    """A source that misses one barrier is not waited for again (bounded step time afterwards) and its stale staging
+    slot is never read again; the sticky error bit stays up for the host watchdog."""
+    import time
+    from dps_b200.ops import _lib as L
+    W = 2
+    model, layout, ps, flat0 = _setup(W, mode="sync", lr=0.1)
+    ps.timeout_ns = int(0.25e9)
+    gen = lambda s: torch.randn(layout.total, device="cuda", generator=torch.Generator("cuda").manual_seed(s)) * 0.05
+    # round 0: both sources arrive
+    g0 = [gen(0), gen(1)]
+    for r in range(W):
+        ps.grad[r].copy_(g0[r])
+    ps.push_sync(); ps.step += 1
+    torch.cuda.synchronize()
+    p = flat0 - 0.1 * (g0[0].half().float() + g0[1].half().float()) / 2
+    # round 1: owner 0 never sees source 1's arrival (as if rank 1 had died before this push)
+    g1 = [gen(2), gen(3)]
+    for r in range(W):
+        ps.grad[r].copy_(g1[r])
+    ps.flags[0][L.F_ARRIVE + 1] -= ps.ctas
+    torch.cuda.synchronize()
+    t0 = time.time(); ps.push_sync(); ps.step += 1; torch.cuda.synchronize(); t_timeout = time.time() - t0
+    assert t_timeout >= 0.2
+    assert int(ps.flag_words(0)[L.F_ALIVE]) == 0b01 and int(ps.flag_words(1)[L.F_ALIVE]) == 0b11
+    assert ps.error_bits(0) & L.ERR_BARRIER_TIMEOUT and ps.error_bits(1) == 0
+    want = layout.to_shards(p)
+    both = (g1[0].half().float() + g1[1].half().float()) / 2
+    want0 = want[0] - 0.1 * layout.to_shards(g1[0].half().float())[0]          # owner 0: mean over the present source
+    want1 = want[1] - 0.1 * layout.to_shards(both)[1]
+    got = layout.to_shards(ps.gather_master())
+    assert torch.allclose(got[0], want0, rtol=1e-5, atol=1e-6) and torch.allclose(got[1], want1, rtol=1e-5, atol=1e-6)
+    # round 2: owner 0 no longer waits for source 1 -> no second timeout
+    g2 = [gen(4), gen(5)]
+    for r in range(W):
+        ps.grad[r].copy_(g2[r])
+    t0 = time.time(); ps.push_sync(); ps.step += 1; torch.cuda.synchronize(); t_after = time.time() - t0
+    assert t_after < 0.1, t_after
+    got2 = layout.to_shards(ps.gather_master())
+    assert torch.allclose(got2[0], want0 - 0.1 * layout.to_shards(g2[0].half().float())[0], rtol=1e-5, atol=1e-6)
+    ps.close()
