@@ -33,7 +33,7 @@ def _decl() -> None:
     L.declare("dps_bn_backward", i32, [P, P, P, P, P, P, P, P, P, P, P, i64, i32, i32, P])
     L.declare("dps_bn_backward_apply", i32, [P, P, P, P, P, P, P, P, P, i64, i32, P])
     L.declare("dps_head_forward_backward", i32, [P] * 12 + [i32, i32, i32, i32, i32, P])
-    L.declare("dps_stem_im2col", i32, [P, P, i32, i32, i32, P])
+    L.declare("dps_stem_im2col", i32, [P, P, i32, i32, i32, P, i32, P])
     _declared = True
 
 
@@ -214,9 +214,9 @@ class ResNetEngine:
             bn.bsums = self.scratch[off + 2 * Cc: off + 4 * Cc]
 
         # ---------------- forward schedule ----------------
-        self.fwd.append(lambda: self.scratch.zero_())
-        im2col = lambda: L.check(self.lib.dps_stem_im2col(_p(self.images), _p(self.col), N, S, S, self._stream()),
-                                 "stem_im2col")
+        # first launch of a step: input staging for the stem, which also clears the per-step statistics scratch
+        im2col = lambda: L.check(self.lib.dps_stem_im2col(_p(self.images), _p(self.col), N, S, S, _p(self.scratch),
+                                                          self.scratch.numel(), self._stream()), "stem_im2col")
         self.fwd.append(im2col)
         self.evalf.append(im2col)
         # layer groups of the segmented pull: [small params + stem + layer1 | layer2 | layer3 | layer4 | fc]
@@ -331,13 +331,13 @@ class ResNetEngine:
         self._side_plans |= {id(p_w0)}
         self._keep.append(p_w0)
         self.bwd.append(_GroupDone(self, 0))
-        # launches per step (bn_backward and head are two kernels each)
+        # launches per step (bn_backward is two kernels)
         self.kernels_per_step = self._count_kernels()
 
     def _count_kernels(self) -> int:
         n_bn = len(self.bns)
         n_conv = len(self.units)
-        fwd = 1 + 1 + n_conv + n_bn + 2                      # memset, im2col, convs, bn, head(2)
+        fwd = 1 + n_conv + n_bn + 1                          # im2col (+ scratch clear), convs, bn, head
         n_dgrad = n_conv - 1
         bwd = 2 * self.n_bn_full + self.n_bn_apply + n_conv + n_dgrad     # (group markers launch nothing themselves)
         return fwd + bwd

@@ -62,13 +62,16 @@ int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x, const 
 
 /* ---- fused head: avg-pool + Linear + softmax cross-entropy, forward and backward (reference:
  *      server.py:56-57,73-75; worker.py:133,341-345).  act: [N][HW][F] bf16; w: [K][F] bf16; out[0] = mean loss,
- *      out[1] = number of correct top-1 predictions.  dlogits scratch is [N][128]; dw/db are accumulated. ---- */
+ *      out[1] = number of correct top-1 predictions.  dlogits scratch is [N][128]; dw/db are accumulated.
+ *      One launch of <= 128 co-resident CTAs with a grid barrier inside: launches on one device must not overlap.
+ *      F must be a multiple of 128 (<= 512), K <= 128. ---- */
 int dps_head_forward_backward(const void* act, const void* w, const float* bias, const long long* labels,
                               float* pooled, float* dlogits, float* loss_n, int* correct_n, void* d_act, float* dw,
                               float* db, float* out, int N, int HW, int F, int K, int training, void* stream);
 
-/* ---- stem input staging: fp32 NCHW images -> bf16 im2col rows [N*H*W][64] (27 valid columns) ---- */
-int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* stream);
+/* ---- stem input staging: fp32 NCHW images -> bf16 im2col rows [N*H*W][64] (27 valid columns, K order (r, s, c)).
+ *      zero / zero_words: optional buffer of 64-bit words cleared by the same launch (the step's BN scratch). ---- */
+int dps_stem_im2col(const float* img, void* col, int N, int H, int W, void* zero, int zero_words, void* stream);
 
 /* ---- device-resident input pipeline (reference: src/workers/worker.py:146-158 transforms, :181-187 DataLoader):
  *      out[b] = Normalize(ToTensor(Flip(Crop(ZeroPad(src[idx[b]], pad))))) as fp32 NCHW, out_labels[b] = src_labels[idx[b]].

@@ -23,7 +23,7 @@ def _lib():
     lib.dps_head_forward_backward.restype = i32
     lib.dps_head_forward_backward.argtypes = [P_] * 12 + [i32] * 5 + [P_]
     lib.dps_stem_im2col.restype = i32
-    lib.dps_stem_im2col.argtypes = [P_, P_, i32, i32, i32, P_]
+    lib.dps_stem_im2col.argtypes = [P_, P_, i32, i32, i32, P_, i32, P_]
     return lib, L
 
 
@@ -186,9 +186,11 @@ def test_stem_im2col_vs_unfold(N, S):
     g = torch.Generator(device="cuda").manual_seed(N)
     img = torch.randn(N, 3, S, S, device="cuda", generator=g)
     col = torch.zeros(N * S * S, 64, device="cuda", dtype=torch.bfloat16)
-    rc = lib.dps_stem_im2col(p(img), p(col), N, S, S, C.c_void_p(L.stream_ptr()))
+    scratch = torch.full((1000,), 7, device="cuda", dtype=torch.int64)     # cleared by the same launch
+    rc = lib.dps_stem_im2col(p(img), p(col), N, S, S, p(scratch), 1000, C.c_void_p(L.stream_ptr()))
     assert rc == 0, lib.dps_last_error()
     torch.cuda.synchronize()
+    assert int(scratch.abs().max()) == 0
     # unfold orders columns (c, r, s); the kernel's K order is (r, s, c) to match the K-R-S-C weights
     u = F.unfold(img, 3, padding=1).view(N, 3, 9, S * S).permute(0, 3, 2, 1).reshape(N * S * S, 27)
     assert torch.equal(col[:, :27].float(), u.to(torch.bfloat16).float())
