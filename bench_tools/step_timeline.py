@@ -33,8 +33,8 @@ def label(fn):
     return "head"
 
 
-from dps_b200.models.engine import _GroupDone
-sched = [(label(f), f) for f in eng.fwd + eng.bwd if not isinstance(f, _GroupDone)] + [("push_sync", job.ps.push_sync), ("pull", job.ps.pull)]
+from dps_b200.models.engine import _Marker
+sched = [(label(f), f) for f in eng.fwd + eng.bwd if not isinstance(f, _Marker)] + [("push_sync", job.ps.push_sync), ("pull", job.ps.pull)]
 per = []
 side = torch.cuda.Stream()
 for lab, f in sched:

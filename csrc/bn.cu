@@ -36,7 +36,7 @@ __device__ __forceinline__ uint4 pack8(const V8& r) {
                     pack_bf16x2(r.v[6], r.v[7]));
 }
 
-__global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
+__global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(
     const __nv_bfloat16* __restrict__ x, const long long* __restrict__ stats, const float* __restrict__ gamma,
     const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
     float* __restrict__ save_mean, float* __restrict__ save_rstd, float* __restrict__ running_mean,
@@ -45,6 +45,22 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
   __shared__ float s_scale[kMaxC], s_shift[kMaxC];
   pdl_launch_dependents();
   pdl_wait();
+  // The first batch of activation loads is issued BEFORE the per-channel prologue (statistics -> scale / shift), so
+  // the two dependent L2 round trips of a small layer overlap instead of adding up.
+  constexpr int kUnroll = 4;
+  const int cg = C / 8;
+  const long long nvec = P * cg;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  uint4 xa[kUnroll], ra[kUnroll];
+#pragma unroll
+  for (int j = 0; j < kUnroll; ++j) {
+    const long long vv = v0 + j * stride;
+    if (vv < nvec) {
+      xa[j] = ld_nc_v4(x + vv * 8);
+      if (residual != nullptr) ra[j] = ld_nc_v4(residual + vv * 8);
+    }
+  }
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     float mean, var;
     if (training) {
@@ -72,23 +88,19 @@ __global__ void __launch_bounds__(kBnThreads) bn_fwd_kernel(
   __syncthreads();
   // blockDim (256) is a multiple of C/8, so a thread always lands on the same 8 channels: keep their
   // scale/shift in registers and issue kUnroll independent 16-byte loads per tensor before using any of them.
-  const int cg = C / 8;
-  const long long nvec = P * cg;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = (int)(v0 % cg) * 8;
   float sc[8], sh[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) { sc[i] = s_scale[c0 + i]; sh[i] = s_shift[c0 + i]; }
-  constexpr int kUnroll = 4;
   for (long long v = v0; v < nvec; v += kUnroll * stride) {
-    uint4 xa[kUnroll], ra[kUnroll];
+    if (v != v0) {
 #pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      const long long vv = v + j * stride;
-      if (vv < nvec) {
-        xa[j] = ld_nc_v4(x + vv * 8);
-        if (residual != nullptr) ra[j] = ld_nc_v4(residual + vv * 8);
+      for (int j = 0; j < kUnroll; ++j) {
+        const long long vv = v + j * stride;
+        if (vv < nvec) {
+          xa[j] = ld_nc_v4(x + vv * 8);
+          if (residual != nullptr) ra[j] = ld_nc_v4(residual + vv * 8);
+        }
       }
     }
 #pragma unroll
@@ -174,13 +186,25 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_reduce_kernel(
   }
 }
 
-__global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
+__global__ void __launch_bounds__(kBnThreads, 3) bn_bwd_apply_kernel(
     const __nv_bfloat16* __restrict__ dz, const __nv_bfloat16* __restrict__ x, const float* __restrict__ mean,
     const float* __restrict__ rstd, const float* __restrict__ gamma, const long long* __restrict__ sums,
     __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma, float* __restrict__ dbeta, long long P, int C) {
   __shared__ float s_a[kMaxC], s_b[kMaxC], s_c[kMaxC];   // dx = s_a*dz + s_b*x + s_c
   pdl_launch_dependents();
   pdl_wait();
+  // first batch of loads before the per-channel prologue (see bn_fwd_kernel)
+  constexpr int kUnroll = 4;
+  const int cg = C / 8;
+  const long long nvec = P * cg;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  uint4 ga[kUnroll], xa[kUnroll];
+#pragma unroll
+  for (int j = 0; j < kUnroll; ++j) {
+    const long long vv = v0 + j * stride;
+    if (vv < nvec) { ga[j] = ld_nc_v4(dz + vv * 8); xa[j] = ld_nc_v4(x + vv * 8); }
+  }
   const float invP = 1.f / (float)P;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
     const float sdz = (float)((double)sums[c] * (1.0 / kGradSumScale));
@@ -197,21 +221,17 @@ __global__ void __launch_bounds__(kBnThreads) bn_bwd_apply_kernel(
     }
   }
   __syncthreads();
-  const int cg = C / 8;
-  const long long nvec = P * cg;
-  const long long stride = (long long)gridDim.x * blockDim.x;
-  const long long v0 = (long long)blockIdx.x * blockDim.x + threadIdx.x;
   const int c0 = (int)(v0 % cg) * 8;
   float ka[8], kb[8], kc[8];
 #pragma unroll
   for (int i = 0; i < 8; ++i) { ka[i] = s_a[c0 + i]; kb[i] = s_b[c0 + i]; kc[i] = s_c[c0 + i]; }
-  constexpr int kUnroll = 4;
   for (long long v = v0; v < nvec; v += kUnroll * stride) {
-    uint4 ga[kUnroll], xa[kUnroll];
+    if (v != v0) {
 #pragma unroll
-    for (int j = 0; j < kUnroll; ++j) {
-      const long long vv = v + j * stride;
-      if (vv < nvec) { ga[j] = ld_nc_v4(dz + vv * 8); xa[j] = ld_nc_v4(x + vv * 8); }
+      for (int j = 0; j < kUnroll; ++j) {
+        const long long vv = v + j * stride;
+        if (vv < nvec) { ga[j] = ld_nc_v4(dz + vv * 8); xa[j] = ld_nc_v4(x + vv * 8); }
+      }
     }
 #pragma unroll
     for (int j = 0; j < kUnroll; ++j) {
@@ -302,7 +322,8 @@ DPS_API int dps_bn_backward_apply(const void* dz, const void* x, const float* me
 // Set-up: in host code `g_bn_noalloc_scratch` is only a stand-in for the symbol, not a device address, so
 // its address is resolved with cudaGetSymbolAddress the first time the entry point runs on a device (with
 // that device current), checked, cached per device and then passed to the kernels as an ordinary pointer.
-// Make that first call on each device before starting any stream capture.
+// Make that first call on each device before starting any stream capture.  The per-device cache is indexed by the
+// CURRENT device (cudaGetDevice): the caller must make the device that owns `stream` current before the call.
 // ------------------------------------------------------------------------------------------
 namespace dps {
 constexpr int kNoAllocMaxC = 512;

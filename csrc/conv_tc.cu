@@ -1671,10 +1671,12 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
   }
   if (rc) { delete pl; return rc; }
   pl->grid = dim3(cp.tiles_w * cp.tiles_h * tiles_n, ngemm / pl->block_n, cp.ngroups);
-  cp.nstages = ((long long)pl->grid.x * pl->grid.y * pl->grid.z <= 148) ? kMaxStages : kMinStages;
+  static const int one_wave_stages = [] { const char* e = getenv("DPS_STAGES1"); const int v = e ? atoi(e) : kMaxStages;
+                                         return v < kMinStages ? kMinStages : (v > kMaxStages ? kMaxStages : v); }();
+  cp.nstages = ((long long)pl->grid.x * pl->grid.y * pl->grid.z <= 148) ? one_wave_stages : kMinStages;
   if (pl->pair) {
     const long long ctas = (long long)pl->grid.x * pl->grid.y * pl->grid.z;
-    cp.nstages = ctas <= 148 ? kMaxStages : 4;          // staging needs >= 3 stages of 24 KiB
+    cp.nstages = ctas <= 148 ? (one_wave_stages < 4 ? 4 : one_wave_stages) : 4;          // staging needs >= 3 stages of 24 KiB
   }
   if (pl->halo) {
     cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
@@ -1707,7 +1709,9 @@ DPS_API int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int 
       WgradHaloParams& hp = pl->whp;
       hp.tiles_w = W / 8; hp.tiles_h = H / 8; hp.tiles_n = N;
       hp.ci_chunks = Cin / 64; hp.Cin = Cin; hp.dw_pitch = dw_pitch; hp.dw = dw;
-      hp.nstages = kWhMaxStages;
+      static const int wh_stages = [] { const char* e = getenv("DPS_WH_STAGES"); const int v = e ? atoi(e) : kWhMaxStages;
+                                        return v < 2 ? 2 : (v > kWhMaxStages ? kWhMaxStages : v); }();
+      hp.nstages = wh_stages;
       const int ny = (Cout / 64) * hp.ci_chunks;
       const int total = hp.tiles_w * hp.tiles_h * hp.tiles_n;
       int ns = nsplit > 0 ? nsplit : (148 / ny > 0 ? 148 / ny : 1);

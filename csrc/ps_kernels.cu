@@ -142,18 +142,37 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
   const uint32_t target = (step + 1) * arrivals_per_step;
   for (int o = T.rank_lo; o < T.rank_hi; ++o) {
     if (threadIdx.x < 32) {
-      // warp-parallel poll: lane s watches source s (W <= 32), so a round costs ONE flag latency and a missing
-      // source costs ONE timeout, not W of them in sequence
+      // warp-parallel poll: lane s watches source s (W + extra <= 32), so a round costs ONE flag latency and a
+      // missing source costs ONE timeout, not W of them in sequence.  Sources W.. are remote workers attached through
+      // the gRPC front door (api.DeviceStoreServicer): they take part from round DPS_F_JOIN[x] on, their arrival
+      // counter starts at that round, and the host detaches them by clearing their membership bit (the poll notices).
       const int s = threadIdx.x;
-      const uint32_t alive = T.flags[o][DPS_F_ALIVE];
-      bool ok = false;
-      if (s < W && ((alive >> s) & 1u)) ok = wait_ge(T.flags[o] + DPS_F_ARRIVE + s, target, timeout_ns);
+      uint32_t* f = T.flags[o];
+      const uint32_t alive = f[DPS_F_ALIVE];
+      bool expected = s < W + T.n_extra && ((alive >> s) & 1u);
+      uint32_t tgt = target;
+      if (expected && s >= W) {
+        const uint32_t join = f[DPS_F_JOIN + (s - W)];
+        if ((int32_t)(step - join) < 0) expected = false;
+        else tgt = (step + 1 - join) * arrivals_per_step;
+      }
+      bool ok = false, left = false;
+      if (expected) {
+        const uint32_t* ctr = f + DPS_F_ARRIVE + s;
+        const uint64_t t0 = globaltimer_ns();
+        while (!(ok = (int32_t)(ld_acquire_sys(ctr) - tgt) >= 0)) {
+          __nanosleep(64);
+          if (s >= W && !((ld_acquire_sys(f + DPS_F_ALIVE) >> s) & 1u)) { left = true; break; }   // detached by the host
+          if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) break;
+        }
+      }
       const uint32_t present = __ballot_sync(0xffffffffu, ok);
+      const uint32_t gone = __ballot_sync(0xffffffffu, expected && !ok && !left);
       if (s == 0) {
-        if (present != alive) {                                // somebody we still counted on did not arrive
-          atomicOr(T.flags[o] + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
-          atomicOr(T.flags[o] + DPS_F_MISSING, alive & ~present);
-          atomicAnd(T.flags[o] + DPS_F_ALIVE, present);
+        if (gone) {                                            // somebody we still counted on did not arrive
+          atomicOr(f + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
+          atomicOr(f + DPS_F_MISSING, gone);
+          atomicAnd(f + DPS_F_ALIVE, ~gone);
         }
         s_present = present;
       }
@@ -165,7 +184,7 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     float* mom = T.mom[o];
     for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
       F8 g = {};
-      for (int s = 0; s < W; ++s) {
+      for (int s = 0; s < W + T.n_extra; ++s) {
         if (!((present >> s) & 1u)) continue;
         if (compress_fp16) {
           acc_f16x8(g, ld_v4(T.stage[o] + (long long)s * E + l), 1.0f);
@@ -481,14 +500,17 @@ __global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__
   const long long per = ((E / VEC + G - 1) / G) * VEC;
   const long long lo = (long long)b * per, hi = min(E, lo + per);
   const uint32_t* of = T.flags[o];
-  __shared__ uint32_t s_seq, s_ok;
+  __shared__ uint32_t s_seq, s_ok, s_ver;
   for (int attempt = 0; attempt < 4; ++attempt) {
     if (threadIdx.x == 0) {
       uint32_t s0 = ld_acquire_sys(of + DPS_F_PUBSEQ);
       int spins = 0;
       while ((s0 & 1u) && spins++ < (1 << 16)) { __nanosleep(64); s0 = ld_acquire_sys(of + DPS_F_PUBSEQ); }
       s_seq = s0;
-      if (b == 0) T.flags[r][DPS_F_SEEN + o] = ld_acquire_sys(of + DPS_F_VERSION);
+      // the version that goes with this sequence value: read AFTER the sequence, before the copy; it is recorded as
+      // "seen" only if the sequence is unchanged after the copy, so a worker never reports a newer version than the
+      // data it holds (that would under-state the staleness of its next push)
+      s_ver = ld_acquire_sys(of + DPS_F_VERSION);
     }
     __syncthreads();
     for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
@@ -499,8 +521,15 @@ __global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__
     __syncthreads();
     if (threadIdx.x == 0) {
       __threadfence_system();
-      s_ok = (ld_acquire_sys(of + DPS_F_PUBSEQ) == s_seq) ? 1u : 0u;
-      if (!s_ok && attempt == 3) atomicAdd(T.flags[r] + DPS_F_TORN_PULLS, 1u);
+      // an odd sequence (the owner was still rewriting when the bounded spin gave up) is a failed attempt even if it
+      // has not changed since
+      s_ok = ((s_seq & 1u) == 0u && ld_acquire_sys(of + DPS_F_PUBSEQ) == s_seq) ? 1u : 0u;
+      if (s_ok && b == 0) T.flags[r][DPS_F_SEEN + o] = s_ver;
+      if (!s_ok && attempt == 3) {
+        atomicAdd(T.flags[r] + DPS_F_TORN_PULLS, 1u);
+        // keep the OLDEST version any attempt saw: over-stating staleness is safe, under-stating it is not
+        if (b == 0) atomicMin(T.flags[r] + DPS_F_SEEN + o, s_ver);
+      }
     }
     __syncthreads();
     if (s_ok) break;
@@ -532,7 +561,8 @@ DPS_API const char* dps_last_error(void) { return g_dps_err; }
 static int check_tables(const DpsTables* T) {
   if (!T) DPS_FAIL(1, "null tables");
   if (T->world < 1 || T->world > DPS_MAX_RANKS) DPS_FAIL(1, "world %d out of range", T->world);
-  if (T->rank_lo < 0 || T->rank_hi > T->world || T->rank_lo >= T->rank_hi) DPS_FAIL(1, "bad rank range");
+  if (T->n_extra < 0 || T->world + T->n_extra > DPS_MAX_RANKS) DPS_FAIL(1, "world + extra sources exceeds %d", DPS_MAX_RANKS);
+  if (T->rank_lo < 0 || T->rank_hi > T->world + T->n_extra || T->rank_lo >= T->rank_hi) DPS_FAIL(1, "bad rank range");
   if (T->block_elems <= 0 || T->block_elems % 8 != 0) DPS_FAIL(1, "block_elems must be a positive multiple of 8");
   if (T->shard_elems <= 0 || T->shard_elems % T->block_elems != 0) DPS_FAIL(1, "shard_elems must be a multiple of block_elems");
   return 0;

@@ -236,6 +236,8 @@ class Worker:
             # dgrad / BatchNorm chain of the backward pass; only the first layer group + the reduce stay exposed
             self._wstream = torch.cuda.Stream(device=job.device)
             self.engine.side_stream = self._wstream
+            self._xstream = torch.cuda.Stream(device=job.device)     # projection shortcuts beside their block
+            self.engine.branch_stream = self._xstream
             self.engine.on_group_done = self._send_group
             nseg = self.ps.nseg
             self._send_ctas = [self.ps.send_ctas(k) for k in range(nseg)]
@@ -426,8 +428,7 @@ class Worker:
             with _R("forward"):
                 self._pre()
                 if native:
-                    for f in self.engine.fwd:
-                        f()
+                    self.engine._run(self.engine.fwd)
             ev[2].record()
             with _R("backward"):
                 if native:

@@ -72,6 +72,8 @@ class Config:
     overlap_pull: bool = True             # sync mode: pull at step start, overlapped with forward per layer group
     overlap_push: bool = True             # sync mode: weight gradients + per-group push on a side stream during backward
     async_ring_slots: int = 4             # ring depth per (owner, worker) pair
+    serve_port: Optional[int] = None      # device path: rank 0 also serves the gRPC contract on this port (0 = any free)
+    remote_slots: int = 0                 # source slots for remote workers attached through that door (sync mode)
     # ---- outputs -----------------------------------------------------------
     metrics_dir: Optional[str] = None     # write METRICS_JSON records to files here
     checkpoint: Optional[str] = None

@@ -41,7 +41,14 @@ def _p(t: Optional[torch.Tensor]) -> Optional[int]:
     return None if t is None else t.data_ptr()
 
 
-class _GroupDone:
+class _Marker:
+    """Schedule entries that launch nothing themselves (fork / join of a side branch, push hooks)."""
+
+    def __call__(self) -> None:
+        pass
+
+
+class _GroupDone(_Marker):
     """Marker in the backward schedule: every weight gradient of layer group `k` has been issued."""
 
     def __init__(self, engine: "ResNetEngine", k: int):
@@ -50,6 +57,14 @@ class _GroupDone:
     def __call__(self) -> None:
         if self.engine.on_group_done is not None:
             self.engine.on_group_done(self.k)
+
+
+class _Fork(_Marker):
+    """The entries up to the matching _Join that are tagged for the branch stream run beside the main chain."""
+
+
+class _Join(_Marker):
+    pass
 
 
 @dataclass
@@ -95,6 +110,7 @@ class ResNetEngine:
         # set by the worker: weight gradients (which nothing in the backward chain consumes) run on `side_stream`,
         # and `on_group_done(k)` is called there once every weight gradient of layer group k has been issued
         self.side_stream: Optional[torch.cuda.Stream] = None
+        self.branch_stream: Optional[torch.cuda.Stream] = None
         self.on_group_done: Optional[Callable[[int], None]] = None
 
     # ------------------------------------------------------------------ helpers
@@ -156,7 +172,7 @@ class ResNetEngine:
                     wname=prefix_conv + ".weight", residual=residual)
         return unit
 
-    def _finalize_unit_fwd(self, u):
+    def _finalize_unit_fwd(self, u, join_before_bn: bool = False):
         """Create plans (needs bn.stats allocated) and append forward / eval launches."""
         bn = u["bn"]
         kw = dict(N=self.N, H=u["H"], W=u["H"], Cin=u["Cin"], Cout=u["Cout"], R=u["R"], stride=u["stride"])
@@ -169,6 +185,8 @@ class ResNetEngine:
         u["fprop"] = plan
         res = u["residual"]
         self.fwd.append(plan.run)
+        if join_before_bn:
+            self.fwd.append(_Join())
         self.fwd.append(lambda bn=bn, u=u, res=res: self._bn_fwd(bn, u["c"], u["a"], res, u["relu"], True))
         self.evalf.append(plan_eval.run)
         self.evalf.append(lambda bn=bn, u=u, res=res: self._bn_fwd(bn, u["c"], u["a"], res, u["relu"], False))
@@ -227,11 +245,23 @@ class ResNetEngine:
         for bi, blk in enumerate(blocks):
             if bi > 0 and bi % BLOCKS_PER_STAGE == 0:
                 first_of_group[id(blk["u1"])] = bi // BLOCKS_PER_STAGE
+        # A projection shortcut (1x1 conv + BN) depends only on the block input: it runs on the branch stream beside
+        # conv1 / bn1 / conv2 of its block and is joined in front of bn2, which adds it as the residual.
+        self._branch_ids = set()
+        shortcut_of = {id(b["u1"]): b["us"] for b in blocks if b["us"] is not None}
+        joins_before_bn = {id(b["u2"]) for b in blocks if b["us"] is not None}
         for u in units:
+            if any(u is s for s in shortcut_of.values()):
+                continue                                        # emitted with its block's conv1 below
             if id(u) in first_of_group:
                 k = first_of_group[id(u)]
                 self.fwd.append(lambda k=k: self.seg_wait(k) if self.seg_wait is not None else None)
-            self._finalize_unit_fwd(u)
+            if id(u) in shortcut_of:
+                self.fwd.append(_Fork())
+                n0 = len(self.fwd)
+                self._finalize_unit_fwd(shortcut_of[id(u)])
+                self._branch_ids |= {id(f) for f in self.fwd[n0:]}
+            self._finalize_unit_fwd(u, join_before_bn=id(u) in joins_before_bn)
         self.fwd.append(lambda: self.seg_wait(4) if self.seg_wait is not None else None)
 
         # head
@@ -289,6 +319,21 @@ class ResNetEngine:
                 bn_apply(u2["bn"], g_out, u2["c"], g_c2)
             else:
                 bn_full(u2["bn"], g_out, u2["a"], u2["c"], g_out, g_c2, True)
+            if us is not None:
+                # projection shortcut: BN backward, weight gradient and the half-resolution input gradient depend only
+                # on the masked block gradient dz2 -> branch stream, joined in front of conv1's stride-2 dgrad
+                g_cs = self._bf(N, Ho, Ho, Cout)
+                g_s = self._bf(N, Ho, Ho, Cin)
+                self.bwd.append(_Fork())
+                n0 = len(self.bwd)
+                bn_full(us["bn"], dz2, None, us["c"], None, g_cs, False)
+                kws = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=1, stride=stride)
+                p_ws = ConvPlan.wgrad(blk["x"], g_cs, self._g(us["wname"]), **kws)
+                p_ds = ConvPlan.dgrad(g_cs, self._w(us["wname"]), g_s, N=N, H=Ho, W=Ho, Cin=Cin, Cout=Cout, R=1,
+                                      stride=1)
+                self.bwd += [p_ws.run, p_ds.run]
+                self._branch_ids |= {id(f) for f in self.bwd[n0:]}
+                self._keep += [p_ws, p_ds]
             kw2 = dict(N=N, H=Ho, W=Ho, Cin=Cout, Cout=Cout, R=3, stride=1)
             p_w2 = ConvPlan.wgrad(u1["a"], g_c2, self._g(u2["wname"]), **kw2)
             p_d2 = fuse(ConvPlan.dgrad(g_c2, self._w(u2["wname"]), g_a1, **kw2), u1)
@@ -305,20 +350,12 @@ class ResNetEngine:
                 self.bwd.append(p_d1.run)
                 self._keep.append(p_d1)
             else:
-                # projection shortcut: its gradient is computed at half resolution first and added by the
-                # stride-2 dgrad of conv1 at the pixels of parity (0,0)
-                g_cs = self._bf(N, Ho, Ho, Cout)
-                g_s = self._bf(N, Ho, Ho, Cin)
-                bn_full(us["bn"], dz2, None, us["c"], None, g_cs, False)
-                kws = dict(N=N, H=H, W=H, Cin=Cin, Cout=Cout, R=1, stride=stride)
-                p_ws = ConvPlan.wgrad(blk["x"], g_cs, self._g(us["wname"]), **kws)
-                p_ds = ConvPlan.dgrad(g_cs, self._w(us["wname"]), g_s, N=N, H=Ho, W=Ho, Cin=Cin, Cout=Cout, R=1,
-                                      stride=1)
+                # the shortcut's gradient (branch above) is at half resolution: the stride-2 dgrad of conv1 adds it at
+                # the pixels of parity (0,0)
                 p_d1 = ConvPlan.dgrad(g_c1, self._w(u1["wname"]), g_x, addend=g_s, **kw1).addend_compact(True)
                 fuse(p_d1, prev_unit)
-                self.bwd += [p_ws.run, p_ds.run, p_d1.run]
-                self._side_plans |= {id(p_ws)}
-                self._keep += [p_ws, p_ds, p_d1]
+                self.bwd += [_Join(), p_d1.run]
+                self._keep += [p_d1]
             g_out, g_out_fused = g_x, True
             if bi > 0 and bi % BLOCKS_PER_STAGE == 0:            # first block of layer (bi/2 + 1): group complete
                 self.bwd.append(_GroupDone(self, bi // BLOCKS_PER_STAGE))
@@ -350,29 +387,49 @@ class ResNetEngine:
     def _on_side(self, f) -> bool:
         return isinstance(f, _GroupDone) or id(getattr(f, "__self__", None)) in self._side_plans
 
-    def backward(self) -> None:
-        """Backward schedule.  With a side stream, weight gradients (and the per-group push hooks) are forked onto it
-        right after the kernel that produced their input and joined at the end: nothing in the dgrad / BatchNorm
-        chain depends on them, so they fill the bubbles between the kernels of that chain."""
-        W = self.side_stream
-        if W is None:
-            for f in self.bwd:
-                f()
-            return
+    def _run(self, sched) -> None:
+        """Run a schedule.  Without side streams everything goes to the current stream in list order (a valid serial
+        order).  With them: entries of a _Fork.._Join section that belong to the branch run on `branch_stream`
+        (projection shortcuts, beside the block's main path); weight gradients and the per-group push hooks run on
+        `side_stream`, forked right after the kernel that produced their input and joined at the end -- nothing in
+        the dgrad / BatchNorm chain depends on them, so they fill the bubbles between the kernels of that chain."""
+        W, X = self.side_stream, self.branch_stream
         cur = torch.cuda.current_stream()
-        for f in self.bwd:
-            if self._on_side(f):
+        forked = used_w = False
+        for f in sched:
+            if isinstance(f, _Fork):
+                if X is not None:
+                    X.wait_stream(cur)
+                    forked = True
+            elif isinstance(f, _Join):
+                if forked:
+                    cur.wait_stream(X)
+                    forked = False
+            elif X is not None and id(f) in self._branch_ids:
+                if W is not None and self._on_side(f):           # the shortcut's weight gradient: input comes from X
+                    W.wait_stream(X)
+                    used_w = True
+                    with torch.cuda.stream(W):
+                        f()
+                else:
+                    with torch.cuda.stream(X):
+                        f()
+            elif W is not None and self._on_side(f):
                 W.wait_stream(cur)
+                used_w = True
                 with torch.cuda.stream(W):
                     f()
             else:
                 f()
-        cur.wait_stream(W)
+        if used_w:                       # (a stream that took no work must not be joined inside a graph capture)
+            cur.wait_stream(W)
+
+    def backward(self) -> None:
+        self._run(self.bwd)
 
     def forward_backward(self) -> None:
-        for f in self.fwd:
-            f()
-        self.backward()
+        self._run(self.fwd)
+        self._run(self.bwd)
 
     def forward_eval(self) -> None:
         for f in self.evalf:

@@ -25,7 +25,7 @@ F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS, F_DROPPED, F_ALIVE, F_P
 F_HEARTBEAT, F_RING_TAIL, F_RING_HEAD, F_VERSION, F_PUBSEQ, F_APPLY_DONE = 64, 96, 97, 98, 99, 100
 F_SLOTS = 128
 F_STAT_ACCEPTED, F_STAT_REJECTED, F_STAT_SUM, F_STAT_MAX, F_STAT_HIST, F_STAT_LAST = 512, 513, 514, 515, 520, 544
-F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT, F_SEGEXPECT = 640, 704, 800, 864, 880
+F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT, F_SEGEXPECT, F_JOIN = 640, 704, 800, 864, 880, 896
 ERR_BARRIER_TIMEOUT, ERR_PULL_TIMEOUT, ERR_RING_FULL = 1, 2, 4
 
 _P = C.c_void_p
@@ -35,7 +35,7 @@ _PtrArray = _P * MAX_RANKS
 class DpsTables(C.Structure):
     _fields_ = [
         ("world", C.c_int32), ("rank_lo", C.c_int32), ("rank_hi", C.c_int32),
-        ("block_elems", C.c_int32), ("ring_slots", C.c_int32), ("pad_", C.c_int32),
+        ("block_elems", C.c_int32), ("ring_slots", C.c_int32), ("n_extra", C.c_int32),
         ("shard_elems", C.c_int64), ("n_small", C.c_int64),
         ("grad", _PtrArray), ("master", _PtrArray), ("mom", _PtrArray), ("stage", _PtrArray),
         ("ring", _PtrArray), ("wbf16", _PtrArray), ("small", _PtrArray), ("pub", _PtrArray),

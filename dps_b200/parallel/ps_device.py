@@ -46,10 +46,18 @@ class DevicePS:
         self.ctas = _default_ctas(self.E)
         self.async_ctas = max(1, min(self.ctas, 128 // world))
         self.timeout_ns = int((timeout_s if timeout_s is not None else cfg.barrier_timeout_s) * 1e9)
+        # remote workers attached through the gRPC front door are extra SOURCES of the sync push: they get a staging
+        # slot on every owner after the W on-box workers, and the master shards move into the peer-visible arena so
+        # that the rank hosting the door can read all of them without a collective
+        self.n_extra = int(cfg.remote_slots) if cfg.mode == "sync" else 0
+        if world + self.n_extra > L.MAX_RANKS:
+            raise ValueError(f"workers + remote_slots must be <= {L.MAX_RANKS}")
 
         spec = ArenaSpec()
         spec.add("flags", L.FLAG_WORDS * 4)
-        spec.add("stage", world * self.E * (2 if self.compress else 4))
+        spec.add("stage", (world + self.n_extra) * self.E * (2 if self.compress else 4))
+        if self.n_extra:
+            spec.add("master", self.E * 4)
         spec.add("wbf16", self.total * 2)
         spec.add("small", max(self.n_small, 8) * 4)
         if self.is_async:
@@ -64,8 +72,10 @@ class DevicePS:
         dev = self.device
         self.grad: Dict[int, torch.Tensor] = {r: torch.zeros(self.total, dtype=torch.float32, device=dev)
                                               for r in self.local}
-        self.master: Dict[int, torch.Tensor] = {r: torch.zeros(self.E, dtype=torch.float32, device=dev)
-                                                for r in self.local}
+        if self.n_extra:
+            self.master: Dict[int, torch.Tensor] = {r: self.fabric.tensor(r, "master", torch.float32) for r in self.local}
+        else:
+            self.master = {r: torch.zeros(self.E, dtype=torch.float32, device=dev) for r in self.local}
         self.mom: Dict[int, torch.Tensor] = {r: torch.zeros(self.E, dtype=torch.float32, device=dev)
                                              for r in self.local}
         self.wbf16 = {r: self.fabric.tensor(r, "wbf16", torch.bfloat16) for r in self.local}
@@ -75,7 +85,7 @@ class DevicePS:
             self.flags[r][L.F_ALIVE] = (1 << world) - 1 if world < 32 else -1
 
         t = L.DpsTables()
-        t.world, t.block_elems, t.ring_slots = world, layout.block_elems, self.R
+        t.world, t.block_elems, t.ring_slots, t.n_extra = world, layout.block_elems, self.R, self.n_extra
         t.shard_elems, t.n_small = self.E, self.n_small
         t.rank_lo, t.rank_hi = (0, world) if emulate else (rank, rank + 1)
         for r in range(world):
@@ -183,6 +193,55 @@ class DevicePS:
         backward kernels it runs beside."""
         n = int(self._seg[seg + 1]) - int(self._seg[seg])
         return int(max(1, min(148, n // (256 * 8 * 4))))
+
+    # ---- remote sources (gRPC front door) ---------------------------------------------------
+    def peer_flags(self, r: int) -> torch.Tensor:
+        """Flag block of ANY rank as seen from this device (peer mapping): host-side membership commands."""
+        return self.fabric.tensor(r, "flags", torch.int32)
+
+    def peer_master(self, r: int) -> torch.Tensor:
+        assert self.n_extra, "master shards are peer-visible only when remote_slots > 0"
+        return self.fabric.tensor(r, "master", torch.float32)
+
+    def snapshot_master(self) -> torch.Tensor:
+        """Full fp32 arena read from every owner's shard over the peer mappings (no collective: callable from the
+        thread that serves an RPC).  Consistent when the caller is in lock-step with the round (a remote sync worker
+        between its push and its next push); otherwise shards may differ by one round."""
+        shards = torch.stack([self.peer_master(r).clone() for r in range(self.world)])
+        return self.layout.from_shards(shards)
+
+    def attach_source(self, x: int, join_round: int) -> None:
+        """Extra source x (rank W+x) takes part in the sync rounds >= join_round on every owner."""
+        bit = 1 << (self.world + x)
+        for r in range(self.world):
+            f = self.peer_flags(r)
+            f[L.F_JOIN + x] = join_round
+            f[L.F_ARRIVE + self.world + x] = 0
+        torch.cuda.synchronize(self.device)
+        for r in range(self.world):
+            f = self.peer_flags(r)
+            f[L.F_ALIVE] = int(f[L.F_ALIVE]) | bit
+        torch.cuda.synchronize(self.device)
+
+    def detach_source(self, x: int) -> None:
+        """Stop waiting for extra source x.  An owner already polling for it notices the cleared bit."""
+        bit = 1 << (self.world + x)
+        for r in range(self.world):
+            f = self.peer_flags(r)
+            f[L.F_ALIVE] = int(f[L.F_ALIVE]) & ~bit
+        torch.cuda.synchronize(self.device)
+
+    def push_remote(self, x: int, grad_flat: torch.Tensor, arrivals: int, stream=None) -> None:
+        """SEND half of the push for extra source x from this device: `grad_flat` (fp32 arena order, device tensor of
+        layout.total elements; zeroed by the kernel) goes to slot W+x of every owner, `arrivals` signals per owner."""
+        t = L.DpsTables.from_buffer_copy(self.tables)
+        t.rank_lo, t.rank_hi = self.world + x, self.world + x + 1
+        t.grad[self.world + x] = grad_flat.data_ptr()
+        t.step_ctr = None                               # the heartbeat value is informational for a remote source
+        cfg = self.cfg
+        L.check(self.lib.dps_push_segment(C.byref(t), 0, cfg.lr, cfg.momentum, cfg.weight_decay, int(self.compress),
+                                          arrivals, self.timeout_ns, 0, self.E, self.SEND, arrivals,
+                                          L.stream_ptr(stream)), "push_remote")
 
     def pull(self, stream=None, wait: bool = True) -> None:
         L.check(self.lib.dps_pull_bcast(self._tp, self.step, self.ctas, L.stream_ptr(stream)), "pull_bcast")

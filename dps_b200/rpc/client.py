@@ -57,6 +57,7 @@ class DistributedWorker:
         self.train_loader = self.test_loader = None
         self.channel = None
         self.stub: Optional[proto.ParameterServerStub] = None
+        self._chan_lock = threading.Lock()
         self.local_step_counter = 0
         self.global_step_cache = 0
         self.training_start_time: Optional[float] = None
@@ -88,19 +89,32 @@ class DistributedWorker:
                     raise
                 time.sleep(backoff_base ** attempt)
 
+    def ping(self, timeout: float = 10.0) -> int:
+        """Cheap liveness RPC: a FetchParameters whose request metadata asks for an EMPTY payload (this framework's
+        server honours it and still refreshes `last_seen`; the reference server would answer with the full 45 MB).
+        Returns the server's global step."""
+        rep = self.stub.FetchParameters(proto.FetchRequest(worker_id=self.worker_id), timeout=timeout,
+                                        metadata=(("dps-ping", "1"),))
+        return int(rep.global_step)
+
     def start_heartbeat(self, period_s: float = 30.0) -> None:
-        """Liveness ping; reconnects the channel (same id) on failure."""
+        """Liveness ping (reference: the health-check loop that is never started, worker.py:112-126); reconnects the
+        channel (same worker id) on failure.  The stub is swapped under a lock and the old channel is closed."""
         def loop():
             while self.training_active:
                 time.sleep(period_s)
                 if not self.training_active:
                     break
                 try:
-                    self.stub.FetchParameters(proto.FetchRequest(worker_id=self.worker_id), timeout=10)
+                    self.ping()
                 except grpc.RpcError:
                     try:
-                        self.channel = proto.make_channel(self.server_address)
-                        self.stub = proto.ParameterServerStub(self.channel)
+                        channel = proto.make_channel(self.server_address)
+                        stub = proto.ParameterServerStub(channel)
+                        with self._chan_lock:
+                            old, self.channel, self.stub = self.channel, channel, stub
+                        if old is not None:
+                            old.close()
                     except Exception:
                         pass
         self._hb_thread = threading.Thread(target=loop, daemon=True)

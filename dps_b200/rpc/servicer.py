@@ -138,6 +138,10 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             self.opt.velocity[k] = np.array(v.numpy() if hasattr(v, "numpy") else v, dtype=np.float32, copy=True)
         self._resume_step = int(resume_side.get("global_step", 0))
         self._last_ckpt_step = self._resume_step
+        self._ckpt_lock = threading.Lock()
+        self._ckpt_written_step = -1
+        self._ckpt_threads: List[threading.Thread] = []
+        self.checkpoint_errors = 0
 
         # membership
         self.registration_lock = threading.Lock()
@@ -189,9 +193,46 @@ class ParameterServerServicer(proto.ParameterServerServicer):
             self._fetch_cache.clear()
             due = (self.cfg.checkpoint and self.cfg.checkpoint_every > 0
                    and self.global_step - self._last_ckpt_step >= self.cfg.checkpoint_every)
+            snap = None
+            if due:
+                # claim this checkpoint while still holding the lock (two concurrent async pushes must not both see
+                # `due`) and take the snapshot here; the file is written by a background thread so that neither the
+                # push RPC nor -- in sync mode -- the workers parked on the barrier wait for 45 MB of disk I/O
+                self._last_ckpt_step = self.global_step
+                snap = self._snapshot_locked()
         self.update_times.append(time.time() - t0)
-        if due:
-            self.save_checkpoint()
+        if snap is not None:
+            t = threading.Thread(target=self._write_checkpoint, args=(self.cfg.checkpoint, snap), daemon=True,
+                                 name="dps-ckpt")
+            self._ckpt_threads = [x for x in self._ckpt_threads if x.is_alive()] + [t]
+            t.start()
+
+    def wait_for_checkpoints(self, timeout: Optional[float] = None) -> None:
+        """Block until every periodic checkpoint that has been claimed so far is on disk."""
+        for t in list(self._ckpt_threads):
+            t.join(timeout)
+
+    def _snapshot_locked(self) -> dict:
+        return {"state": {k: np.array(v, copy=True) for k, v in self.parameters.items()},
+                "momentum": {k: np.array(v, copy=True) for k, v in self.opt.velocity.items()},
+                "step": self.global_step, "total_updates": self.total_updates}
+
+    def _write_checkpoint(self, path: str, snap: dict) -> Optional[str]:
+        """One writer at a time; an I/O failure is logged and never fails the push that triggered the save."""
+        from ..utils import checkpoint as CK
+        try:
+            with self._ckpt_lock:
+                if snap["step"] < self._ckpt_written_step:          # a newer snapshot is already on disk
+                    return None
+                CK.save(path, snap["state"], global_step=snap["step"], momentum=snap["momentum"],
+                        config=self.cfg.to_dict(), extra={"mode": self.mode, "total_updates": snap["total_updates"]})
+                self._ckpt_written_step = snap["step"]
+            self._log(f"checkpoint written to {path} at global step {snap['step']}")
+            return path
+        except Exception as e:                                       # noqa: BLE001 - disk full, permissions, ...
+            self.checkpoint_errors += 1
+            self._log(f"checkpoint to {path} failed: {e!r}")
+            return None
 
     def save_checkpoint(self, path: Optional[str] = None) -> Optional[str]:
         """state_dict-compatible checkpoint (loads into the reference ResNet18 with strict=True) + resume sidecar
@@ -200,16 +241,11 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         path = path or self.cfg.checkpoint
         if not path:
             return None
-        from ..utils import checkpoint as CK
         with self.param_lock:
-            state = {k: np.array(v, copy=True) for k, v in self.parameters.items()}
-            mom = {k: np.array(v, copy=True) for k, v in self.opt.velocity.items()}
-            step = self.global_step
-            self._last_ckpt_step = step
-        CK.save(path, state, global_step=step, momentum=mom, config=self.cfg.to_dict(),
-                extra={"mode": self.mode, "total_updates": self.total_updates})
-        self._log(f"checkpoint written to {path} at global step {step}")
-        return path
+            snap = self._snapshot_locked()
+            self._last_ckpt_step = snap["step"]
+        self.wait_for_checkpoints()
+        return self._write_checkpoint(path, snap)
 
     def aggregate_gradients_sync(self, worker_gradients: List[Dict[str, np.ndarray]]):
         return mean_gradients(worker_gradients)
@@ -284,8 +320,18 @@ class ParameterServerServicer(proto.ParameterServerServicer):
                 self._fetch_cache[as_pickle] = cached
             return cached
 
+    @staticmethod
+    def _is_ping(context) -> bool:
+        """A FetchParameters sent with metadata ('dps-ping', '1') is a liveness ping: no payload wanted."""
+        try:
+            return any(k == "dps-ping" for k, _ in (context.invocation_metadata() or ()))
+        except Exception:
+            return False
+
     def FetchParameters(self, request, context):
         self._touch(request.worker_id)
+        if context is not None and self._is_ping(context):
+            return proto.FetchReply(parameters=b"", global_step=self.global_step)
         step, payload, _ = self._fetch_payload()
         return proto.FetchReply(parameters=payload, global_step=step)
 
@@ -293,6 +339,8 @@ class ParameterServerServicer(proto.ParameterServerServicer):
         """Same RPC for the gRPC runtime: the reply is the cached, already-serialized message (every worker of a round
         gets the same bytes; no per-request copy of the 45 MB payload on the server)."""
         self._touch(request.worker_id)
+        if context is not None and self._is_ping(context):
+            return proto.encode_fetch_reply_wire(b"", self.global_step)
         return self._fetch_payload()[2]
 
     def PushGradrients(self, request, context):

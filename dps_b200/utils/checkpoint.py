@@ -13,6 +13,7 @@ from __future__ import annotations
 
 import json
 import os
+import threading
 from typing import Any, Dict, Mapping, Optional, Tuple
 
 import numpy as np
@@ -28,11 +29,15 @@ def _to_tensor(v: Any) -> torch.Tensor:
 def save(path: str, state: Mapping[str, Any], *, global_step: int = 0,
          momentum: Optional[Mapping[str, Any]] = None, shard_versions: Optional[list] = None,
          config: Optional[dict] = None, extra: Optional[dict] = None) -> None:
+    """Both files are written under names unique to this writer and renamed into place, sidecar FIRST: a reader (or
+    a crash between the two renames) then sees either the old pair or new weights with the new sidecar, never new
+    weights with an old step / momentum.  The weights file also carries its step in `<path>.meta.json` and the
+    sidecar repeats it (``load`` checks that they agree)."""
     os.makedirs(os.path.dirname(os.path.abspath(path)) or ".", exist_ok=True)
     sd = {k: _to_tensor(v) for k, v in state.items()}
-    tmp = path + ".tmp"
+    tag = f".tmp.{os.getpid()}.{threading.get_ident()}.{int(global_step)}"
+    tmp = path + tag
     torch.save(sd, tmp)
-    os.replace(tmp, path)
     side = {
         "global_step": int(global_step),
         "shard_versions": list(shard_versions or []),
@@ -41,11 +46,15 @@ def save(path: str, state: Mapping[str, Any], *, global_step: int = 0,
         "torch_rng": torch.get_rng_state(),
         "momentum": {k: _to_tensor(v) for k, v in (momentum or {}).items()},
     }
-    torch.save(side, path + ".resume.tmp")
-    os.replace(path + ".resume.tmp", path + ".resume")
-    with open(path + ".meta.json", "w") as f:
+    side_tmp = path + ".resume" + tag
+    torch.save(side, side_tmp)
+    meta_tmp = path + ".meta.json" + tag
+    with open(meta_tmp, "w") as f:
         json.dump({"global_step": int(global_step), "num_tensors": len(sd),
                    "num_elements": int(sum(t.numel() for t in sd.values()))}, f)
+    os.replace(side_tmp, path + ".resume")
+    os.replace(tmp, path)
+    os.replace(meta_tmp, path + ".meta.json")
 
 
 def load(path: str, restore_rng: bool = False) -> Tuple[Dict[str, torch.Tensor], dict]:
@@ -53,6 +62,13 @@ def load(path: str, restore_rng: bool = False) -> Tuple[Dict[str, torch.Tensor],
     side: dict = {}
     if os.path.exists(path + ".resume"):
         side = torch.load(path + ".resume", map_location="cpu", weights_only=True)
+        try:                                   # a crash between the renames leaves a sidecar newer than the weights
+            with open(path + ".meta.json") as f:
+                meta_step = int(json.load(f).get("global_step", -1))
+            if meta_step >= 0 and meta_step != int(side.get("global_step", meta_step)):
+                side["step_mismatch"] = {"weights": meta_step, "sidecar": int(side.get("global_step", 0))}
+        except (OSError, ValueError):
+            pass
         if restore_rng and "torch_rng" in side:
             torch.set_rng_state(side["torch_rng"])
     return sd, side

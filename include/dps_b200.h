@@ -49,6 +49,7 @@ extern "C" {
 #define DPS_F_DROP 832          /* [32] local: this step's push to owner o was skipped            */
 #define DPS_F_SEGCOUNT 864      /* [16] segmented pull: deliveries received per layer group           */
 #define DPS_F_SEGEXPECT 880     /* [16] segmented pull: deliveries expected so far per layer group    */
+#define DPS_F_JOIN 896          /* [32] first sync round in which extra source x (rank W+x) takes part  */
 #define DPS_MAX_SEGS 16
 #define DPS_FLAG_WORDS 1024
 
@@ -66,7 +67,7 @@ typedef struct DpsTables {
   int32_t rank_hi;
   int32_t block_elems;    /* BS: block-cyclic sharding granule                         */
   int32_t ring_slots;     /* R: async ring depth per owner                             */
-  int32_t pad_;
+  int32_t n_extra;        /* extra source slots after the W on-box workers (remote workers of the gRPC door) */
   int64_t shard_elems;    /* E: elements per shard (multiple of BS)                    */
   int64_t n_small;        /* arena prefix also delivered in fp32 (BN affine, fc bias)  */
   float* grad[DPS_MAX_RANKS];            /* worker: fp32 gradient arena [W*E]                    */

@@ -55,7 +55,9 @@ int dps_bn_backward_apply(const void* dz, const void* x, const float* mean, cons
  * only receive their inputs and outputs): the scratch is a built-in device array, max C = 512 channels
  * (8 KiB per GPU, held until exit).  It is cleared on `stream` at the start of every call; calls that overlap
  * on the GPU race on it.  The first call on a device resolves the array's address -- make it before any
- * stream capture.  Larger C is rejected with an error.  Same outputs as dps_bn_backward. */
+ * stream capture.  The array that is used belongs to the device that is CURRENT when the call is made, so the
+ * device that owns `stream` must be the current device (a stream of another GPU would be handed the wrong
+ * GPU's array).  Larger C is rejected with an error.  Same outputs as dps_bn_backward. */
 int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x, const float* mean, const float* rstd,
                             const float* gamma, void* dz, void* dx, float* dgamma, float* dbeta, long long P, int C,
                             int relu, void* stream);

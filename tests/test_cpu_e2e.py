@@ -157,7 +157,8 @@ def test_server_checkpoint_and_resume(tmp_path, ref_modules):
 
     for s in range(3):
         push(sv, s)
-    # periodic checkpoint after step 2; the file loads into the REFERENCE model, strict
+    # periodic checkpoint after step 2 (written by a background thread); the file loads into the REFERENCE model, strict
+    sv.wait_for_checkpoints()
     sd, side = CK.load(ck)
     assert side["global_step"] == 2 and set(side["momentum"]) == set(names)
     ref_model = ref_modules["server"].ResNet18(num_classes=100)
@@ -221,3 +222,58 @@ def test_injected_worker_crash_is_survived_on_the_grpc_path(tmp_path):
     assert 4 <= sv.global_step <= 5 and 1 not in sv.active_workers
     assert sv.barrier_timeouts <= 1                               # eviction, not a timeout per round
     assert time.time() - t0 < 100
+
+
+def test_concurrent_async_pushes_claim_a_periodic_checkpoint_once(tmp_path):
+    """Async mode, checkpoint_every=1, eight pushes racing on eight threads: every due checkpoint is claimed by exactly
+    one push under the parameter lock, writers are serialised, tmp names are unique, no push fails, and the file on disk
+    ends up at the last claimed step with a matching sidecar."""
+    import threading
+    from dps_b200.rpc import codec, proto
+    from dps_b200.utils import checkpoint as CK
+    ck = str(tmp_path / "async.pt")
+    cfg = Config(mode="async", workers=8, lr=0.01, checkpoint=ck, checkpoint_every=1, staleness_bound=100)
+    sv = S.ParameterServerServicer("async", 8, 0.01, staleness_bound=100, config=cfg)
+    names = [k for k, v in sv.parameters.items() if v.dtype == np.float32 and "running" not in k][:4]
+    g = {k: np.full(sv.parameters[k].shape, 1e-3, dtype=np.float32) for k in names}
+    payload = codec.encode_any(codec.compress_gradients(g, "fp16"), False)
+    ids = [sv.RegisterWorker(proto.RegisterRequest(worker_ip=str(i)), None).worker_id for i in range(8)]
+    results = []
+
+    def work(wid):
+        r = sv.PushGradrients(proto.PushRequest(worker_id=wid, gradients=payload, local_step=0), None)
+        results.append(r.received)
+
+    ts = [threading.Thread(target=work, args=(w,)) for w in ids]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    sv.wait_for_checkpoints()
+    assert results == [True] * 8 and sv.global_step == 8 and sv.checkpoint_errors == 0
+    sd, side = CK.load(ck)
+    assert "step_mismatch" not in side and 1 <= side["global_step"] <= 8
+    assert side["global_step"] == sv._ckpt_written_step
+    assert not [f for f in __import__("os").listdir(tmp_path) if ".tmp." in f]          # nothing left behind
+
+
+def test_heartbeat_ping_is_a_cheap_rpc_and_refreshes_liveness():
+    """The client's liveness ping is a FetchParameters with request metadata that makes the server answer with an EMPTY
+    payload (the first version fetched all 45 MB every 30 s) and still counts as a sign of life."""
+    import time
+    from dps_b200.rpc import proto
+    cfg = Config(mode="sync", workers=1, lr=0.1)
+    server, sv, port = S.build_server(cfg.replace(port=0), bind="127.0.0.1")
+    server.start()
+    try:
+        w = DistributedWorker(f"127.0.0.1:{port}", "w0", config=cfg)
+        w.connect_to_server()
+        seen0 = sv.registered_workers[w.worker_id]["last_seen"]
+        time.sleep(0.05)
+        assert w.ping() == 0
+        assert sv.registered_workers[w.worker_id]["last_seen"] > seen0
+        rep = w.stub.FetchParameters(proto.FetchRequest(worker_id=w.worker_id), metadata=(("dps-ping", "1"),))
+        assert len(rep.parameters) == 0
+        full = w.stub.FetchParameters(proto.FetchRequest(worker_id=w.worker_id))
+        assert len(full.parameters) > 40_000_000
+        w.cleanup()
+    finally:
+        server.stop(0)

@@ -6,8 +6,10 @@ that only gets its inputs and outputs.  The library then reduces into a built-in
 (at most 512 channels) that every call shares and that still holds the previous call's sums, so the
 entry point has to clear it itself.  This test drives the C ABI directly with ctypes and checks, on two
 calls in a row with different shapes and data, that the results equal those of the existing
-dps_bn_backward (which is given a fresh zeroed scratch each time).  The file name sorts last on
-purpose: if it fails under `-x`, every other test has already run.
+dps_bn_backward (which is given a fresh zeroed scratch each time) and, independently of that sibling, those
+of a plain fp32 PyTorch restatement of BatchNorm + ReLU backward -- a bug shared by both entry points would
+pass the first comparison but not the second.  The file name sorts last on purpose: if it fails under `-x`,
+every other test has already run.
 """
 import ctypes as C
 
@@ -56,6 +58,18 @@ def _run(lib, L, noalloc, x, y, dy, mean, rstd, gamma, P, Cc):
     return dz, dx, dgamma, dbeta
 
 
+def _torch_oracle(x, y, dy, mean, rstd, gamma):
+    """fp32 restatement: dz = dy * (y > 0); dbeta = sum dz; dgamma = sum dz * xhat;
+    dx = gamma * rstd * (dz - mean(dz) - xhat * mean(dz * xhat))."""
+    xf, dyf = x.float(), dy.float()
+    dz = dyf * (y.float() > 0).float()
+    xhat = (xf - mean) * rstd
+    P = xf.shape[0]
+    dbeta, dgamma = dz.sum(0), (dz * xhat).sum(0)
+    dx = gamma * rstd * (dz - dbeta / P - xhat * dgamma / P)
+    return dz, dx, dgamma, dbeta
+
+
 def test_noalloc_bn_backward_matches_existing_entry_point_twice_in_a_row():
     lib, L = _lib()
     # second call: fewer channels and other data -- stale sums from the first call would show up here
@@ -68,6 +82,10 @@ def test_noalloc_bn_backward_matches_existing_entry_point_twice_in_a_row():
                 assert torch.allclose(a.float(), b.float(), rtol=1.5e-2, atol=1e-3), (name, Cc)
             else:
                 assert torch.allclose(a, b, rtol=1e-5, atol=1e-6), (name, Cc)
+        ref = _torch_oracle(*case)
+        for name, a, b in zip(("dz", "dx", "dgamma", "dbeta"), got, ref):
+            tol = 1.5e-2 * float(b.abs().max()) + 1e-3
+            assert float((a.float() - b).abs().max()) <= tol, (name, Cc, float((a.float() - b).abs().max()), tol)
 
 
 def test_noalloc_rejects_channel_counts_beyond_the_built_in_scratch():
