@@ -44,6 +44,7 @@ def parse_args(argv=None):
     p.add_argument("--engine", choices=["native", "torch"], default="native",
                    help="torch = BASELINE arm: same PS kernels, ATen/cuDNN compute (bench_tools/torch_engine.py)")
     p.add_argument("--momentum", type=float, default=0.0)
+    p.add_argument("--staleness-policy", choices=["reference", "world", "batch"], default="reference")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="eager launches (for ncu launch lists)")
     return p.parse_args(argv)
@@ -105,7 +106,7 @@ def run_ours(args) -> dict:
     local = int(os.environ.get("LOCAL_RANK", rank))
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     cfg = Config(mode=args.mode, workers=world, batch_size=args.batch, lr=0.1, momentum=args.momentum,
-                 image_size=args.image_size, barrier_timeout_s=30.0,
+                 image_size=args.image_size, barrier_timeout_s=30.0, staleness_policy=args.staleness_policy,
                  use_cuda_graph=not args.no_graph)
     factory = None
     if args.engine == "torch":
@@ -183,6 +184,17 @@ def run_ours(args) -> dict:
                "api": "dps_b200.api.Job.worker.train_step(pinned images, pinned labels) -> LossHandle.item()"}
 
     err = job.ps.error_bits()
+    async_info = None
+    if cfg.mode == "async":
+        wk.drain()
+        st = job.ps.async_stats()
+        tot = max(1, st["async_updates"] + st["rejected_updates"])
+        async_info = {"staleness_policy": cfg.staleness_policy, "staleness_bound": cfg.staleness_bound,
+                      "shard0_accepted": st["async_updates"], "shard0_rejected": st["rejected_updates"],
+                      "shard0_rejection_rate": round(st["rejected_updates"] / tot, 4),
+                      "shard0_mean_staleness": round(st["running_mean_staleness"], 3),
+                      "dropped_pushes_rank0": st["dropped_pushes"], "torn_pulls_rank0": st["torn_pulls"],
+                      "owner_stream": "dedicated" if wk.async_server else "worker"}
     value = K * B * world / (ms_dev / 1e3)
     # data-path launches per step, counted while the step graph was captured (eager path: the documented counts)
     ps_launches = getattr(wk, "ps_launches_per_step", None) or ((8 if wk.overlap_pull else 3) if cfg.mode == "sync" else 4)
@@ -202,7 +214,7 @@ def run_ours(args) -> dict:
                          % (2 * wk.engine.activation_bytes() / 1e6 if hasattr(wk.engine, "activation_bytes") else 0),
                    "baseline_number": "%.1f img/s = reference %s run published in BASELINE.md" % (
                        PUBLISHED[cfg.mode], "sync 4-worker" if cfg.mode == "sync" else "async 8-worker")},
-        "clocks": clocks, "e2e": e2e,
+        "clocks": clocks, "e2e": e2e, "async": async_info,
         "gpu_launches": int(K * (kernels - 1 + ps_launches)) if kernels else 0,
         "ps_error_bits": err,
     }

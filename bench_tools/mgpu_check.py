@@ -12,13 +12,14 @@ from dps_b200 import Config
 from dps_b200.api import Job
 
 mode, out_path = sys.argv[1], sys.argv[2]
-B, steps = 16, 3
+B, steps = 16, (int(sys.argv[3]) if len(sys.argv) > 3 else 3)
 cfg = Config(mode=mode, batch_size=B, lr=0.05, barrier_timeout_s=20.0, use_cuda_graph=True)
 job = Job(cfg)
 rank, world, dev = job.rank, job.world, job.device
 g = torch.Generator().manual_seed(100 + rank)
-xs = [torch.randn(B, 3, 32, 32, generator=g).pin_memory() for _ in range(steps)]
-ys = [torch.randint(0, 100, (B,), generator=g).pin_memory() for _ in range(steps)]
+nb = min(steps, 8)
+xs = [torch.randn(B, 3, 32, 32, generator=g).pin_memory() for _ in range(nb)]
+ys = [torch.randint(0, 100, (B,), generator=g).pin_memory() for _ in range(nb)]
 
 extra = {}
 if mode == "sync":
@@ -37,8 +38,11 @@ if mode == "sync":
     for k, v in job.worker.engine.bn_buffers().items():   # undo the oracle pass's running-stat update
         v.copy_(job.model_cpu.state_dict()[k].to(v.device))
 losses = []
+vers = []
 for i in range(steps):
-    losses.append(job.worker.train_step(xs[i], ys[i]).item())
+    losses.append(job.worker.train_step(xs[i % nb], ys[i % nb]).item())
+    if mode == "async" and i % 5 == 0:
+        vers.append(job.ps.version())          # shard version counters only move forward
     if mode == "sync" and i == 0:
         got = job.ps.gather_master()
         extra["max_abs_diff_vs_single_process_mean_step"] = float((got - want).abs().max())
@@ -62,15 +66,21 @@ dist.broadcast(ref0, 0)
 same = torch.tensor([int(torch.equal(ref0, mine) and torch.equal(mine, master.to(torch.bfloat16)))], device=dev)
 dist.all_reduce(same, op=dist.ReduceOp.MIN)
 st = job.ps.async_stats() if mode == "async" else {"async_updates": 0, "rejected_updates": 0}
-info = torch.tensor([job.ps.error_bits(), job.ps.version(), st["async_updates"], st["rejected_updates"]],
-                    device=dev, dtype=torch.int64)
+hist = st.get("staleness_histogram", {})
+mono = int(all(b >= a for a, b in zip(vers, vers[1:])))
+info = torch.tensor([job.ps.error_bits(), job.ps.version(), st["async_updates"], st["rejected_updates"],
+                     st.get("dropped_pushes", 0), st.get("torn_pulls", 0), sum(hist.values()),
+                     st.get("running_max_staleness", 0), mono], device=dev, dtype=torch.int64)
 allinfo = [torch.zeros_like(info) for _ in range(world)]
 dist.all_gather(allinfo, info)
 if rank == 0:
     res = {"mode": mode, "steps": steps, "losses": losses, "replicas_equal": bool(same.item()),
            "finite": bool(torch.isfinite(master).all()), "error_bits": [int(t[0]) for t in allinfo],
            "versions": [int(t[1]) for t in allinfo], "accepted": [int(t[2]) for t in allinfo],
-           "rejected": [int(t[3]) for t in allinfo], **extra}
+           "rejected": [int(t[3]) for t in allinfo], "dropped": [int(t[4]) for t in allinfo],
+           "torn_pulls": [int(t[5]) for t in allinfo], "hist_total": [int(t[6]) for t in allinfo],
+           "max_staleness": [int(t[7]) for t in allinfo], "versions_monotone": [int(t[8]) for t in allinfo],
+           "world": world, "staleness_bound": cfg.staleness_bound, **extra}
     with open(out_path, "w") as f:
         json.dump(res, f)
     print(json.dumps(res))

@@ -63,6 +63,8 @@ __device__ __forceinline__ void acc_f16x8(F8& a, uint4 h, float w) {
   f = unpack_f16x2(h.w); a.v[6] += w * f.x; a.v[7] += w * f.y;
 }
 
+__device__ __forceinline__ uint32_t owner_mask(int W) { return W >= 32 ? 0xffffffffu : ((1u << W) - 1u); }
+
 // Spin until *flag >= target (acquire, system scope).  Returns false on timeout.
 __device__ __forceinline__ bool wait_ge(const uint32_t* flag, uint32_t target, unsigned long long timeout_ns) {
   if ((int32_t)(ld_acquire_sys(flag) - target) >= 0) return true;
@@ -72,6 +74,30 @@ __device__ __forceinline__ bool wait_ge(const uint32_t* flag, uint32_t target, u
     if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) return false;
   }
   return true;
+}
+
+// Remote sources (gRPC front door): once per round and owner, ONE thread decides which attached remote workers have a
+// complete, not yet consumed gradient in their staging slot (arrival counter >= (consumed + 1) * signals per push), marks
+// them in DPS_F_INCLUDE for the reduce that follows in the same stream, and records the consuming round.
+__global__ void remote_gate_kernel(const __grid_constant__ DpsTables T, uint32_t step_arg, uint32_t arrivals_per_push) {
+  if (threadIdx.x != 0 || blockIdx.x != 0) return;
+  const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
+  for (int o = T.rank_lo; o < T.rank_hi && o < T.world; ++o) {
+    uint32_t* f = T.flags[o];
+    const uint32_t alive = f[DPS_F_ALIVE];
+    uint32_t mask = 0;
+    for (int x = 0; x < T.n_extra; ++x) {
+      const int s = T.world + x;
+      if (!((alive >> s) & 1u)) continue;
+      const uint32_t consumed = f[DPS_F_CONSUMED + x];
+      if ((int32_t)(ld_acquire_sys(f + DPS_F_ARRIVE + s) - (consumed + 1) * arrivals_per_push) >= 0) {
+        mask |= 1u << s;
+        f[DPS_F_CONSUMED + x] = consumed + 1;
+        f[DPS_F_CONSUMED_ROUND + x] = step;
+      }
+    }
+    f[DPS_F_INCLUDE] = mask;
+  }
 }
 
 // ------------------------------------------------------------------------------------------
@@ -144,30 +170,20 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     if (threadIdx.x < 32) {
       // warp-parallel poll: lane s watches source s (W + extra <= 32), so a round costs ONE flag latency and a
       // missing source costs ONE timeout, not W of them in sequence.  Sources W.. are remote workers attached through
-      // the gRPC front door (api.DeviceStoreServicer): they take part from round DPS_F_JOIN[x] on, their arrival
-      // counter starts at that round, and the host detaches them by clearing their membership bit (the poll notices).
+      // the gRPC front door (rpc/device_door.py): the owners never WAIT for them -- a CPU worker needs seconds per
+      // step -- they are folded into whichever round is current once their gradient has arrived completely; that
+      // decision is taken once per round by remote_gate_kernel (launched in front of this kernel) and read here from
+      // DPS_F_INCLUDE, so all CTAs of the owner agree.
       const int s = threadIdx.x;
       uint32_t* f = T.flags[o];
+      if (b == 0 && s == 0) st_relaxed_sys(f + DPS_F_ROUND, step);      // host-visible progress
       const uint32_t alive = f[DPS_F_ALIVE];
-      bool expected = s < W + T.n_extra && ((alive >> s) & 1u);
-      uint32_t tgt = target;
-      if (expected && s >= W) {
-        const uint32_t join = f[DPS_F_JOIN + (s - W)];
-        if ((int32_t)(step - join) < 0) expected = false;
-        else tgt = (step + 1 - join) * arrivals_per_step;
-      }
-      bool ok = false, left = false;
-      if (expected) {
-        const uint32_t* ctr = f + DPS_F_ARRIVE + s;
-        const uint64_t t0 = globaltimer_ns();
-        while (!(ok = (int32_t)(ld_acquire_sys(ctr) - tgt) >= 0)) {
-          __nanosleep(64);
-          if (s >= W && !((ld_acquire_sys(f + DPS_F_ALIVE) >> s) & 1u)) { left = true; break; }   // detached by the host
-          if (timeout_ns && globaltimer_ns() - t0 > timeout_ns) break;
-        }
-      }
+      const bool expected = s < W && ((alive >> s) & 1u);
+      bool ok = false;
+      if (expected) ok = wait_ge(f + DPS_F_ARRIVE + s, target, timeout_ns);
+      if (s >= W && s < W + T.n_extra) ok = (f[DPS_F_INCLUDE] >> s) & 1u;
       const uint32_t present = __ballot_sync(0xffffffffu, ok);
-      const uint32_t gone = __ballot_sync(0xffffffffu, expected && !ok && !left);
+      const uint32_t gone = __ballot_sync(0xffffffffu, expected && !ok);
       if (s == 0) {
         if (gone) {                                            // somebody we still counted on did not arrive
           atomicOr(f + DPS_F_ERROR, DPS_ERR_BARRIER_TIMEOUT);
@@ -178,6 +194,9 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
       }
     }
     __syncthreads();
+    // device-side timing of the update itself (after the barrier wait): CTA 0's span is accumulated in DPS_F_UPDATE_NS
+    // so the server metrics report a measured average update time (reference: update_times, server.py:121,128,140-143)
+    const uint64_t t_upd0 = (b == 0 && threadIdx.x == 0) ? globaltimer_ns() : 0;
     const uint32_t present = s_present;
     const float inv = 1.0f / (float)max(1, __popc(present));
     float* master = T.master[o];
@@ -214,7 +233,10 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
       store_f32x8(master + l, p);
     }
     __syncthreads();
-    if (threadIdx.x == 0 && b == 0) T.flags[o][DPS_F_VERSION] += 1;   // shard version (survives checkpoint resume)
+    if (threadIdx.x == 0 && b == 0) {
+      T.flags[o][DPS_F_VERSION] += 1;   // shard version (survives checkpoint resume)
+      *reinterpret_cast<unsigned long long*>(T.flags[o] + DPS_F_UPDATE_NS) += globaltimer_ns() - t_upd0;
+    }
   }
 }
 
@@ -296,7 +318,7 @@ __global__ void wait_seg_kernel(const __grid_constant__ DpsTables T, int rank, i
   if (threadIdx.x == 0) {
     (void)step_arg;
     uint32_t* f = T.flags[rank];
-    const uint32_t live = (uint32_t)__popc(f[DPS_F_ALIVE]);
+    const uint32_t live = (uint32_t)__popc(f[DPS_F_ALIVE] & owner_mask(T.world));   // owners only: extra sources own no shard
     const uint32_t target = f[DPS_F_SEGEXPECT + seg] + ctas_per_owner * live;
     f[DPS_F_SEGEXPECT + seg] = target;
     if (!wait_ge(f + DPS_F_SEGCOUNT + seg, target, timeout_ns)) atomicOr(f + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
@@ -314,7 +336,7 @@ __global__ void wait_pull_kernel(const __grid_constant__ DpsTables T, int rank, 
   if (threadIdx.x == 0) {
     const uint32_t step = T.step_ctr ? T.step_ctr[0] : step_arg;
     uint32_t* f = T.flags[rank];
-    const uint32_t target = f[DPS_F_PULLEXPECT] + ctas_per_owner * (uint32_t)__popc(f[DPS_F_ALIVE]);
+    const uint32_t target = f[DPS_F_PULLEXPECT] + ctas_per_owner * (uint32_t)__popc(f[DPS_F_ALIVE] & owner_mask(T.world));
     f[DPS_F_PULLEXPECT] = target;
     if (!wait_ge(f + DPS_F_PULLCOUNT, target, timeout_ns)) atomicOr(f + DPS_F_ERROR, DPS_ERR_PULL_TIMEOUT);
     if (bump && T.step_ctr) T.step_ctr[0] = step + 1;     // last kernel of the round: safe to advance
@@ -388,13 +410,23 @@ __global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__
 }
 
 // Owner: examine the ring in ticket order, decide accept/reject + weight for each complete arrival.
+// policy (staleness accounting, recorded in the metrics):
+//   0 "reference"   : every accepted update bumps the shard version; reject staleness > bound (server.py:171-186)
+//   1 "world"       : same, but the bound is widened by W - 1: with W workers that each pull once per step, W - 1 other
+//                     updates land between a worker's pull and its push BY CONSTRUCTION, so the reference bound of 5
+//                     silently discards ~40 % of the work at W = 8
+//   2 "batch"       : all arrivals drained in one pass count as ONE version (they were concurrent)
+// bump_step: 1 when the scan runs in the worker's own stream right after its push (the original schedule); 0 when a
+// dedicated server stream drives it (the worker's pull then advances the push counter).
 __global__ void async_scan_kernel(const __grid_constant__ DpsTables T, int o, uint32_t producer_ctas, int bound,
-                                  float alpha, float floor_w, int max_batch) {
+                                  float alpha, float floor_w, int max_batch, int policy, int bump_step) {
   if (threadIdx.x != 0 || blockIdx.x != 0) return;
   uint32_t* f = T.flags[o];
   const uint32_t R = (uint32_t)T.ring_slots;
-  if (T.step_ctr) T.step_ctr[1] += 1;                     // this rank's push (same stream, before) is done
+  if (bump_step && T.step_ctr) T.step_ctr[1] += 1;        // this rank's push (same stream, before) is done
+  if (policy == 1) bound += T.world - 1;
   uint32_t h = f[DPS_F_RING_HEAD], v = f[DPS_F_VERSION];
+  const uint32_t v_pass = v;
   int n = 0, n_apply = 0;
   while (n < max_batch && n < DPS_MAX_PLAN) {
     const uint32_t slot = h % R;
@@ -402,13 +434,13 @@ __global__ void async_scan_kernel(const __grid_constant__ DpsTables T, int o, ui
     if ((int32_t)(ld_acquire_sys(f + DPS_F_SLOTS + slot * 4) - need) < 0) break;
     const uint32_t src = f[DPS_F_SLOTS + slot * 4 + 1];
     const uint32_t seen = f[DPS_F_SLOTS + slot * 4 + 2];
-    const int s = (int)(v - seen);
+    const int s = (int)((policy == 2 ? v_pass : v) - seen);
     float w = 0.0f;
     if (s > bound) {
       f[DPS_F_STAT_REJECTED] += 1;
     } else {
       w = fmaxf(floor_w, 1.0f / (1.0f + alpha * (float)s));
-      v += 1;
+      if (policy != 2 || n_apply == 0) v += 1;
       n_apply += 1;
       f[DPS_F_STAT_ACCEPTED] += 1;
     }
@@ -450,6 +482,7 @@ __global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant_
   __syncthreads();
   bool any = false;
   for (int k = 0; k < n; ++k) any |= (s_w[k] > 0.0f);
+  const uint64_t t_upd0 = (b == 0 && threadIdx.x == 0) ? globaltimer_ns() : 0;
   float* master = T.master[o];
   float* mom = T.mom[o];
   if (any) {
@@ -478,6 +511,7 @@ __global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant_
   }
   __syncthreads();
   if (threadIdx.x == 0) {
+    if (b == 0 && any) *reinterpret_cast<unsigned long long*>(f + DPS_F_UPDATE_NS) += globaltimer_ns() - t_upd0;
     __threadfence();
     const uint32_t done = atomicAdd(f + DPS_F_APPLY_DONE, 1u) + 1;
     if (done == (uint32_t)G) {                                 // last CTA publishes
@@ -492,7 +526,9 @@ __global__ void __launch_bounds__(256) async_apply_kernel(const __grid_constant_
 
 // Worker: gather every owner's published bf16 shard (peer reads) under a per-chunk seq-lock and record
 // the version seen (the `local_step` of the next push, reference worker.py:245,299).  grid = (G, W).
-__global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__ DpsTables T, int r) {
+__global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__ DpsTables T, int r, int bump_step) {
+  // bump_step: this pull follows the rank's push in the same stream and closes its step (dedicated-server schedule)
+  if (bump_step && T.step_ctr && blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) T.step_ctr[1] += 1;
   const int W = T.world, BS = T.block_elems;
   const long long E = T.shard_elems, n_small = T.n_small;
   const int G = gridDim.x, b = blockIdx.x;
@@ -571,6 +607,8 @@ static int check_tables(const DpsTables* T) {
 DPS_API int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
                           int compress_fp16, int ctas, unsigned long long timeout_ns, void* stream) {
   if (int e = check_tables(T)) return e;
+  if (T->n_extra > 0 && T->rank_lo < T->world)
+    remote_gate_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, step, (uint32_t)ctas);
   push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
                                                           timeout_ns, 0, T->shard_elems, 3, (uint32_t)ctas);
   DPS_CHECK(cudaGetLastError());
@@ -585,6 +623,8 @@ DPS_API int dps_push_segment(const DpsTables* T, unsigned step, float lr, float 
     DPS_FAIL(1, "push_segment: bad range [%lld, %lld)", seg_lo, seg_hi);
   if (!(phases & 3)) DPS_FAIL(1, "push_segment: phases must select SEND (1) and/or REDUCE (2)");
   if (ctas < 1) DPS_FAIL(1, "push_segment: ctas must be positive");
+  if ((phases & 2) && T->n_extra > 0 && T->rank_lo < T->world)
+    remote_gate_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, step, arrivals_per_step);
   push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
                                                           timeout_ns, seg_lo, seg_hi, phases, arrivals_per_step);
   DPS_CHECK(cudaGetLastError());
@@ -648,20 +688,40 @@ DPS_API int dps_push_async(const DpsTables* T, int rank, unsigned step, int ctas
 
 DPS_API int dps_async_apply(const DpsTables* T, int owner, int producer_ctas, int staleness_bound, float alpha,
                             float floor_w, int max_batch, float lr, float momentum, float weight_decay, int ctas,
-                            void* stream) {
+                            int policy, int bump_step, void* stream) {
   if (int e = check_tables(T)) return e;
+  if (policy < 0 || policy > 2) DPS_FAIL(1, "async_apply: unknown staleness policy %d", policy);
   async_scan_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, owner, (uint32_t)producer_ctas, staleness_bound, alpha,
-                                                         floor_w, max_batch);
+                                                         floor_w, max_batch, policy, bump_step);
   DPS_CHECK(cudaGetLastError());
   async_apply_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, owner, lr, momentum, weight_decay);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
 
-DPS_API int dps_pull_async(const DpsTables* T, int rank, int ctas, void* stream) {
+DPS_API int dps_pull_async(const DpsTables* T, int rank, int ctas, int bump_step, void* stream) {
   if (int e = check_tables(T)) return e;
   dim3 grid(ctas, T->world);
-  pull_async_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*T, rank);
+  pull_async_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(*T, rank, bump_step);
+  DPS_CHECK(cudaGetLastError());
+  return 0;
+}
+
+// Host-side membership commands on a (possibly peer-mapped) flag word: *word = (*word & and_mask) | or_mask, atomically
+// with respect to the kernels that update the same word (the reduce phase drops dead sources with atomicAnd).
+namespace dps {
+__global__ void flag_update_kernel(uint32_t* word, uint32_t and_mask, uint32_t or_mask) {
+  if (threadIdx.x == 0 && blockIdx.x == 0) {
+    atomicAnd(word, and_mask);
+    if (or_mask) atomicOr(word, or_mask);
+    __threadfence_system();
+  }
+}
+}  // namespace dps
+
+DPS_API int dps_flag_update(uint32_t* word, unsigned and_mask, unsigned or_mask, void* stream) {
+  if (!word) DPS_FAIL(1, "flag_update: null word");
+  flag_update_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(word, and_mask, or_mask);
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

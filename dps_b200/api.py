@@ -34,6 +34,11 @@ def _env_int(name: str, default: int) -> int:
         return default
 
 
+class JobFailure(RuntimeError):
+    """The on-box job cannot continue (a peer missed a barrier / stopped sending heartbeats).  The process exits
+    non-zero and the supervising launcher restarts the job from the last checkpoint (dps_b200.launch --supervise)."""
+
+
 class Job:
     """Bootstraps one rank: process group, symmetric arenas, parameter shard, worker engine."""
 
@@ -47,6 +52,8 @@ class Job:
         self.world = _env_int("WORLD_SIZE", 1) if world is None else world
         self.device_index = _env_int("LOCAL_RANK", self.rank) if device_index is None else device_index
         self.cfg = cfg.replace(workers=self.world).validate()
+        if self.cfg.serve_port is not None and self.cfg.remote_slots == 0 and self.cfg.mode == "sync":
+            self.cfg = self.cfg.replace(remote_slots=1)        # same decision on every rank: it sizes the staging arena
         if not torch.cuda.is_available():
             raise RuntimeError(
                 "dps_b200.api.Job is the on-box device path (one process per B200, NVLink peer memory) and needs CUDA. "
@@ -81,6 +88,41 @@ class Job:
         if self.cfg.resume:
             _, side = CK.load(self.cfg.resume)
             self.server.restore_sidecar(side)
+        self.version_offset = self.ps.version() - self.ps.step      # shard version - round number (resume step)
+        # failure detection: a host thread watches this rank's flag block -- sticky error bits raised by
+        # the bounded waits of the kernels, and peers' heartbeat words -- and marks the job failed; the training loop
+        # then raises JobFailure instead of training on with a rank missing
+        self.failed: Optional[str] = None
+        self.watchdog = None
+        if self.cfg.watchdog and self.world > 1:
+            from .parallel.watchdog import decode_error_bits, for_device_ps, missing_ranks
+            from .ops import _lib as L
+
+            wd_stream = {}
+
+            def on_poll(stale):
+                if "s" not in wd_stream:
+                    wd_stream["s"] = torch.cuda.Stream(device=self.device)
+                with torch.cuda.stream(wd_stream["s"]):
+                    return _on_poll(stale)
+
+            def _on_poll(stale):
+                bits = self.ps.error_bits()
+                if bits and self.failed is None:
+                    miss = missing_ranks(int(self.ps.flag_words()[L.F_MISSING]) & 0xFFFFFFFF, self.world)
+                    self.failed = f"device error bits {decode_error_bits(bits)}, missing ranks {miss}"
+                elif stale and self.failed is None and self.worker.local_step_counter > 0:
+                    self.failed = f"no heartbeat from ranks {stale} for {self.cfg.heartbeat_timeout_s:.0f}s"
+
+            self.watchdog = for_device_ps(self.ps, timeout_s=self.cfg.heartbeat_timeout_s, on_stale=on_poll)
+            self.watchdog.always_notify = True
+            self.watchdog.start(period_s=min(1.0, max(0.05, self.cfg.heartbeat_timeout_s / 10.0)))
+        # gRPC front door onto the device store (reference: the four RPCs of server.py:190-318): rank 0 hosts it
+        self.door = self.door_server = None
+        self.door_port: Optional[int] = None
+        if self.cfg.serve_port is not None and self.rank == 0:
+            from .rpc.device_door import start_door
+            self.door_server, self.door, self.door_port = start_door(self, int(self.cfg.serve_port))
         self.barrier()
 
     def barrier(self) -> None:
@@ -89,7 +131,17 @@ class Job:
             import torch.distributed as dist
             dist.barrier(device_ids=[self.device_index])
 
+    def check_alive(self) -> None:
+        if self.failed is not None:
+            raise JobFailure(f"rank {self.rank}: {self.failed}")
+
     def close(self) -> None:
+        if self.watchdog is not None:
+            self.watchdog.stop()
+            self.watchdog = None
+        if self.door_server is not None:
+            self.door_server.stop(0)
+            self.door_server = None
         self.barrier()
         self.ps.close()
 
@@ -145,6 +197,9 @@ class ParameterServer:
         mine = int(versions[self.job.rank]) if len(versions) == self.job.world else step
         self.ps.flags[self.job.rank][L.F_VERSION] = mine
         torch.cuda.synchronize(self.job.device)
+        # a resumed job continues the step count, so `max_steps` keeps meaning "steps of the whole job"
+        self.job.worker.local_step_counter = step
+        self.job.worker.resumed_from_step = step
 
     def _all_versions(self) -> List[int]:
         v = torch.tensor([self.ps.version()], device=self.job.device, dtype=torch.int64)
@@ -169,11 +224,31 @@ class ParameterServer:
                           "running_mean_staleness": round(st["running_mean_staleness"], 4),
                           "running_max_staleness": st["running_max_staleness"],
                           "staleness_histogram": st["staleness_histogram"], "torn_pulls": st["torn_pulls"],
-                          "dropped_pushes": st["dropped_pushes"]})
+                          "dropped_pushes": st["dropped_pushes"],
+                          "staleness_policy": self.cfg.staleness_policy, "staleness_bound": self.cfg.staleness_bound,
+                          "rejection_rate": round(st["rejected_updates"] / max(1, st["async_updates"] + st["rejected_updates"]), 4),
+                          "owner_stream": "dedicated high-priority stream" if self.job.worker.async_server else "worker stream",
+                          "server_passes": self.ps.server_passes})
+        # update time measured ON THE DEVICE by the reduce / apply kernels themselves (DPS_F_UPDATE_NS)
+        from .ops import _lib as L
+        f = self.ps.flag_words()
+        upd_ns = (int(f[L.F_UPDATE_NS]) & 0xFFFFFFFF) | ((int(f[L.F_UPDATE_NS + 1]) & 0xFFFFFFFF) << 32)
+        done = max(1, steps - self.job.version_offset)
+        extra["average_update_time_us"] = round(upd_ns / done / 1e3, 2)
+        # bytes this shard's owner moved per update and the rate it sustained
+        wk = self.job.worker
+        if wk.local_step_counter > wk.resumed_from_step and sum(wk.epoch_times) > 0:
+            per_step = sum(wk.epoch_times) / (wk.local_step_counter - wk.resumed_from_step)
+            extra["step_time_ms"] = round(per_step * 1e3, 4)
+            for name, nbytes in (("push", self.ps.bytes_per_push()), ("pull", self.ps.bytes_per_pull())):
+                extra[f"{name}_bytes_per_step"] = nbytes
+                # both transfers are overlapped with compute: the rate over the whole step is what the links see
+                extra[f"{name}_GBps_over_step"] = round(nbytes / per_step / 1e9, 2)
+                extra[f"{name}_link_roofline_us"] = round(nbytes / 770e9 * 1e6, 2)      # measured peer-copy rate
         return M.server_final_metrics(mode=self.cfg.mode, total_workers=self.job.world, total_time=total,
                                       global_step=steps, total_updates=steps,
                                       gradients_processed=steps * (self.job.world if self.cfg.mode == "sync" else 1),
-                                      avg_update_time=0.0, learning_rate=self.cfg.lr, extra=extra)
+                                      avg_update_time=upd_ns / done / 1e9, learning_rate=self.cfg.lr, extra=extra)
 
     def finish(self) -> dict:
         """Emit SERVER_FINAL_METRICS exactly once."""
@@ -206,6 +281,8 @@ class Worker:
         self.rank, self.world = job.rank, job.world
         self.worker_id, self.total_workers = job.rank, job.world      # rank == id: never out of range (Q10)
         self.local_step_counter = 0
+        self.resumed_from_step = 0
+        self.fault_step: Optional[int] = None             # test hook (--inject-fault rank:step): die at this step
         self.images_seen = 0
         self.epoch_times: List[float] = []
         self.accuracies: List[float] = []
@@ -231,6 +308,13 @@ class Worker:
             self.ps.set_segments(self.engine.segment_boundaries)
             self.engine.seg_wait = lambda k: self.ps.wait_segment(k)
             self._weights_stale = False
+        if self.cfg.mode == "async" and self.engine_kind == "native" and self.cfg.overlap_push:
+            # async mode: weight gradients and projection shortcuts still run beside the dgrad / BatchNorm chain
+            self._wstream = torch.cuda.Stream(device=job.device)
+            self._xstream = torch.cuda.Stream(device=job.device)
+            self.engine.side_stream, self.engine.branch_stream = self._wstream, self._xstream
+        if self.async_server:
+            self.ps.start_async_server()
         if self.overlap_push:
             # weight gradients and the per-group SEND half of the push run on a second stream beside the
             # dgrad / BatchNorm chain of the backward pass; only the first layer group + the reduce stay exposed
@@ -243,6 +327,11 @@ class Worker:
             self._send_ctas = [self.ps.send_ctas(k) for k in range(nseg)]
             self._arrivals = sum(self._send_ctas)
 
+    @property
+    def arrivals_per_round(self) -> int:
+        """Arrival signals a source sends to every owner per sync round (what the owners' REDUCE counts)."""
+        return self._arrivals if self.overlap_push else self.ps.ctas
+
     # ------------------------------------------------------------------ the step
     @property
     def overlap_pull(self) -> bool:
@@ -251,6 +340,10 @@ class Worker:
         next forward pass)."""
         return (self.cfg.overlap_pull and self.cfg.mode == "sync" and self.engine_kind == "native"
                 and self.cfg.sync_steps == 1)
+
+    @property
+    def async_server(self) -> bool:
+        return self.cfg.mode == "async" and self.cfg.async_server and self.engine_kind == "native"
 
     @property
     def overlap_push(self) -> bool:
@@ -289,6 +382,10 @@ class Worker:
         elif self.cfg.mode == "sync":
             self.ps.push_sync()
             self.ps.pull()
+        elif self.async_server:
+            # the owner role runs on its own stream (DevicePS.start_async_server): the worker only pushes and pulls
+            self.ps.push_async()
+            self.ps.pull_async(bump_step=True)
         else:
             self.ps.push_async()
             self.ps.serve_async()
@@ -357,6 +454,9 @@ class Worker:
         else:
             slot = k
         self._events[slot].record()
+        if self.local_step_counter == self.resumed_from_step:
+            self._events[slot].synchronize()
+            self.first_step_wall = time.time()                # wall clock of this incarnation's first finished step
         self.local_step_counter += 1
         self.images_seen += int(labels.numel())
         return LossHandle(self._ring[slot], self._events[slot])
@@ -515,6 +615,14 @@ class Worker:
                     break
                 last = self.train_step(x, y)
                 taken += 1
+                self.job.check_alive()
+                if self.fault_step is not None and self.local_step_counter >= self.fault_step:
+                    print(f"[dps_b200] FAULT_INJECTED_AT {time.time():.3f} (rank {self.rank}, step "
+                          f"{self.local_step_counter})", flush=True)
+                    os._exit(17)                            # injected fault: the process dies without any clean-up
+                every = self.cfg.checkpoint_every
+                if self.cfg.checkpoint and every > 0 and self.local_step_counter % every == 0:
+                    self.job.server.save_checkpoint(self.cfg.checkpoint)       # collective; same step on every rank
                 if max_steps is not None and self.local_step_counter >= max_steps:
                     done = True
                     break
@@ -528,13 +636,14 @@ class Worker:
                 break
         return self.finish()
 
-    def drain(self, rounds: int = 2) -> None:
+    def drain(self, rounds: int = 3) -> None:
         """Async mode: apply arrivals that landed after this rank's last step (end of job)."""
         if self.cfg.mode != "async":
             return
+        self.ps.stop_async_server()                  # from here on this thread plays the owner role itself
         for _ in range(rounds):
             self.job.barrier()
-            self.ps.serve_async()
+            self.ps.serve_async(bump_step=False)
         self.job.barrier()
 
     def finish(self) -> dict:

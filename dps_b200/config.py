@@ -72,6 +72,9 @@ class Config:
     overlap_pull: bool = True             # sync mode: pull at step start, overlapped with forward per layer group
     overlap_push: bool = True             # sync mode: weight gradients + per-group push on a side stream during backward
     async_ring_slots: int = 4             # ring depth per (owner, worker) pair
+    async_server: bool = True             # async mode: the owner role runs on its own high-priority stream (apply on arrival)
+    async_server_period_us: int = 100     # pause between two scans of the arrival ring by the server thread
+    staleness_policy: str = "reference"   # 'reference' | 'world' (bound + W-1) | 'batch' (one version per drained batch)
     serve_port: Optional[int] = None      # device path: rank 0 also serves the gRPC contract on this port (0 = any free)
     remote_slots: int = 0                 # source slots for remote workers attached through that door (sync mode)
     # ---- outputs -----------------------------------------------------------
@@ -80,6 +83,8 @@ class Config:
     checkpoint_every: int = 0             # gRPC server: also save every N global steps (0 = only at job end)
     resume: Optional[str] = None
     inject_fault: Optional[str] = None    # "rank:step" test hook
+    watchdog: bool = True                 # device path: host thread watching error bits + peer heartbeats
+    heartbeat_timeout_s: float = 30.0     # device path: a peer whose heartbeat word stands still this long is stale
 
     def validate(self) -> "Config":
         if self.mode not in ("sync", "async"):
@@ -96,6 +101,8 @@ class Config:
             raise ValueError("pull_compress must be none|fp16")
         if self.amp not in ("none", "bf16"):
             raise ValueError("amp must be none|bf16")
+        if self.staleness_policy not in ("reference", "world", "batch"):
+            raise ValueError("staleness_policy must be reference|world|batch")
         if self.sync_steps < 1:
             raise ValueError("sync_steps must be >= 1")
         return self
@@ -158,6 +165,14 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--checkpoint-every", type=int, default=0)
     p.add_argument("--resume", default=None)
     p.add_argument("--inject-fault", default=None)
+    p.add_argument("--staleness-policy", choices=["reference", "world", "batch"], default="reference",
+                   help="async mode: reference = reject staleness > bound; world = bound widened by W-1 (W workers put "
+                        "W-1 updates between a pull and the next push by construction); batch = arrivals drained "
+                        "together count as one version")
+    p.add_argument("--serve-port", type=int, default=None,
+                   help="on-box job: rank 0 also serves the gRPC contract on this port (remote / CPU workers)")
+    p.add_argument("--remote-slots", type=int, default=0,
+                   help="on-box sync job: source slots for remote workers attached through --serve-port")
 
 
 def from_args(ns: argparse.Namespace) -> Config:

@@ -22,10 +22,12 @@ FLAG_WORDS = 1024
 
 # flag-block word offsets (mirror include/dps_b200.h)
 F_ARRIVE, F_PULLCOUNT, F_ERROR, F_MISSING, F_TORN_PULLS, F_DROPPED, F_ALIVE, F_PULLEXPECT = 0, 32, 33, 34, 35, 36, 37, 38
+F_UPDATE_NS, F_ROUND = 40, 39
 F_HEARTBEAT, F_RING_TAIL, F_RING_HEAD, F_VERSION, F_PUBSEQ, F_APPLY_DONE = 64, 96, 97, 98, 99, 100
 F_SLOTS = 128
 F_STAT_ACCEPTED, F_STAT_REJECTED, F_STAT_SUM, F_STAT_MAX, F_STAT_HIST, F_STAT_LAST = 512, 513, 514, 515, 520, 544
-F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT, F_SEGEXPECT, F_JOIN = 640, 704, 800, 864, 880, 896
+F_PLAN, F_TICKET, F_SEEN, F_SEGCOUNT, F_SEGEXPECT = 640, 704, 800, 864, 880
+F_CONSUMED, F_CONSUMED_ROUND, F_INCLUDE = 896, 928, 960
 ERR_BARRIER_TIMEOUT, ERR_PULL_TIMEOUT, ERR_RING_FULL = 1, 2, 4
 
 _P = C.c_void_p
@@ -72,9 +74,10 @@ def _declare(lib: C.CDLL) -> None:
         "dps_wait_segment": (i32, [TP, i32, i32, u32, i32, u64, _P]),
         "dps_bump_step": (i32, [TP, _P]),
         "dps_push_async": (i32, [TP, i32, u32, i32, u64, _P]),
-        "dps_async_apply": (i32, [TP, i32, i32, i32, f32, f32, i32, f32, f32, f32, i32, _P]),
-        "dps_pull_async": (i32, [TP, i32, i32, _P]),
+        "dps_async_apply": (i32, [TP, i32, i32, i32, f32, f32, i32, f32, f32, f32, i32, i32, i32, _P]),
+        "dps_pull_async": (i32, [TP, i32, i32, i32, _P]),
         "dps_publish": (i32, [TP, i32, _P]),
+        "dps_flag_update": (i32, [_P, u32, u32, _P]),
     }
     for name, (res, args) in sigs.items():
         fn = getattr(lib, name)

@@ -107,6 +107,10 @@ class DevicePS:
         self.device_counters = False
         self.tables = t
         self._tp = C.byref(self.tables)
+        import threading
+        self._serve_lock = threading.Lock()
+        self._server = None
+        self.server_passes = 0
         self.step = 0                       # sync round / pull sequence number
         self.async_steps = {r: 0 for r in self.local}
         self.launches = 0
@@ -210,26 +214,39 @@ class DevicePS:
         shards = torch.stack([self.peer_master(r).clone() for r in range(self.world)])
         return self.layout.from_shards(shards)
 
-    def attach_source(self, x: int, join_round: int) -> None:
-        """Extra source x (rank W+x) takes part in the sync rounds >= join_round on every owner."""
+    def attach_source(self, x: int) -> None:
+        """Extra source x (rank W+x) may contribute from now on: every owner's per-round gate (remote_gate_kernel)
+        folds its gradient into the round that is current once the gradient has arrived completely.  Runs on the
+        caller's stream and waits only for that stream (the training stream may be busy)."""
         bit = 1 << (self.world + x)
+        cur = torch.cuda.current_stream()
         for r in range(self.world):
             f = self.peer_flags(r)
-            f[L.F_JOIN + x] = join_round
             f[L.F_ARRIVE + self.world + x] = 0
-        torch.cuda.synchronize(self.device)
+            f[L.F_CONSUMED + x] = 0
+        cur.synchronize()
+        for r in range(self.world):
+            self._flag_update(r, L.F_ALIVE, 0xFFFFFFFF, bit)
+        cur.synchronize()
+
+    def remote_progress(self, x: int):
+        """Per owner: (pushes of extra source x consumed so far, round that consumed the latest one, shard version)."""
+        out = []
         for r in range(self.world):
             f = self.peer_flags(r)
-            f[L.F_ALIVE] = int(f[L.F_ALIVE]) | bit
-        torch.cuda.synchronize(self.device)
+            out.append((int(f[L.F_CONSUMED + x]), int(f[L.F_CONSUMED_ROUND + x]), int(f[L.F_VERSION])))
+        return out
 
     def detach_source(self, x: int) -> None:
         """Stop waiting for extra source x.  An owner already polling for it notices the cleared bit."""
         bit = 1 << (self.world + x)
         for r in range(self.world):
-            f = self.peer_flags(r)
-            f[L.F_ALIVE] = int(f[L.F_ALIVE]) & ~bit
-        torch.cuda.synchronize(self.device)
+            self._flag_update(r, L.F_ALIVE, 0xFFFFFFFF & ~bit, 0)
+        torch.cuda.current_stream().synchronize()
+
+    def _flag_update(self, r: int, word: int, and_mask: int, or_mask: int) -> None:
+        L.check(self.lib.dps_flag_update(C.c_void_p(self.fabric.ptr(r, "flags") + 4 * word), and_mask, or_mask,
+                                         L.stream_ptr()), "flag_update")
 
     def push_remote(self, x: int, grad_flat: torch.Tensor, arrivals: int, stream=None) -> None:
         """SEND half of the push for extra source x from this device: `grad_flat` (fp32 arena order, device tensor of
@@ -296,9 +313,10 @@ class DevicePS:
         self.step += 1
 
     # ------------------------------------------------------------------ async
-    def pull_async(self, rank: Optional[int] = None, stream=None) -> None:
+    def pull_async(self, rank: Optional[int] = None, stream=None, bump_step: bool = False) -> None:
         r = self.rank if rank is None else rank
-        L.check(self.lib.dps_pull_async(self._tp, r, self.async_ctas, L.stream_ptr(stream)), "pull_async")
+        L.check(self.lib.dps_pull_async(self._tp, r, self.async_ctas, int(bump_step), L.stream_ptr(stream)),
+                "pull_async")
         self.launches += 1
 
     def push_async(self, rank: Optional[int] = None, stream=None) -> None:
@@ -308,17 +326,56 @@ class DevicePS:
         self.async_steps[r] += 1
         self.launches += 1
 
+    POLICY = {"reference": 0, "world": 1, "batch": 2}
+
     def serve_async(self, owner: Optional[int] = None, lr: Optional[float] = None, stream=None,
-                    max_batch: int = L.MAX_PLAN) -> None:
+                    max_batch: int = L.MAX_PLAN, bump_step: bool = True, ctas: Optional[int] = None) -> None:
         """Owner role: drain the arrival ring (non-blocking) and apply in ticket order."""
         o = self.rank if owner is None else owner
         cfg = self.cfg
-        for _ in range(max(1, (self.world + L.MAX_PLAN - 1) // L.MAX_PLAN)):     # W arrivals per step, 16 per pass
-            L.check(self.lib.dps_async_apply(self._tp, o, self.async_ctas, cfg.staleness_bound, cfg.staleness_alpha,
-                                             cfg.staleness_floor, max_batch, lr if lr is not None else cfg.lr,
-                                             cfg.momentum, cfg.weight_decay, self.ctas, L.stream_ptr(stream)),
-                    "async_apply")
-            self.launches += 2
+        with self._serve_lock:
+            for i in range(max(1, (self.world + L.MAX_PLAN - 1) // L.MAX_PLAN)):     # W arrivals per step, 16 per pass
+                L.check(self.lib.dps_async_apply(self._tp, o, self.async_ctas, cfg.staleness_bound, cfg.staleness_alpha,
+                                                 cfg.staleness_floor, max_batch, lr if lr is not None else cfg.lr,
+                                                 cfg.momentum, cfg.weight_decay, self.ctas if ctas is None else ctas,
+                                                 self.POLICY[cfg.staleness_policy], int(bump_step and i == 0),
+                                                 L.stream_ptr(stream)), "async_apply")
+                self.launches += 2
+
+    # ---- dedicated owner stream (apply on arrival) -------------------------------------------
+    def start_async_server(self) -> None:
+        """The reference's server thread applies a gradient the moment it arrives, whatever the other workers are doing
+        (server.py:290-304).  Here a host thread keeps the owner's scan + apply pair queued on a HIGH-PRIORITY stream
+        of its own, so arrivals are applied while this rank's own forward / backward is still running instead of when
+        its training stream gets there; a slow or stalled worker no longer freezes its shard for everybody else.  The
+        apply uses a bounded number of CTAs so it shares the SMs with the compute kernels."""
+        import threading
+        if self._server is not None:
+            return
+        lo, hi = torch.cuda.Stream.priority_range() if hasattr(torch.cuda.Stream, "priority_range") else (0, -1)
+        self._server_stream = torch.cuda.Stream(device=self.device, priority=-1)
+        self._server_stop = threading.Event()
+        period = max(20, int(self.cfg.async_server_period_us)) * 1e-6
+        ctas = max(8, min(self.ctas, 64))
+
+        def loop():
+            torch.cuda.set_device(self.device)
+            ev = torch.cuda.Event()
+            while not self._server_stop.is_set():
+                self.serve_async(stream=self._server_stream, bump_step=False, ctas=ctas)
+                ev.record(self._server_stream)
+                ev.synchronize()                       # at most one scan + apply pair in flight
+                self.server_passes += 1
+                self._server_stop.wait(period)
+
+        self._server = threading.Thread(target=loop, daemon=True, name="dps-async-server")
+        self._server.start()
+
+    def stop_async_server(self) -> None:
+        if self._server is not None:
+            self._server_stop.set()
+            self._server.join(5.0)
+            self._server = None
 
     # ------------------------------------------------------------------ introspection
     def flag_words(self, rank: Optional[int] = None) -> torch.Tensor:
@@ -351,4 +408,5 @@ class DevicePS:
         return (self.world - 1) * self.E * 2
 
     def close(self) -> None:
+        self.stop_async_server()
         self.fabric.close()

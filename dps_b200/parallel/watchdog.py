@@ -40,6 +40,7 @@ class HeartbeatWatchdog:
     _thread: Optional[threading.Thread] = None
     _stop: threading.Event = field(default_factory=threading.Event)
     on_stale: Optional[Callable[[List[int]], None]] = None
+    always_notify: bool = False           # call on_stale on every poll (the callback also inspects error bits)
 
     def poll(self) -> List[int]:
         now = self.clock()
@@ -55,9 +56,12 @@ class HeartbeatWatchdog:
     def start(self, period_s: float = 1.0) -> None:
         def loop():
             while not self._stop.wait(period_s):
-                stale = self.poll()
-                if stale and self.on_stale is not None:
-                    self.on_stale(stale)
+                try:
+                    stale = self.poll()
+                    if (stale or self.always_notify) and self.on_stale is not None:
+                        self.on_stale(stale)
+                except Exception:                        # the device went away under us: the training loop will notice
+                    pass
         self._thread = threading.Thread(target=loop, daemon=True)
         self._thread.start()
 
@@ -69,9 +73,16 @@ class HeartbeatWatchdog:
 
 def for_device_ps(ps, timeout_s: float = 30.0, on_stale=None) -> HeartbeatWatchdog:
     """Watchdog over a DevicePS: reads the local flag block (a tiny D2H copy) on every poll."""
+    import torch
     from ..ops import _lib as L
+    state = {}
 
     def read():
-        f = ps.flag_words()
+        # private stream: the copy must not queue behind a training stream that is itself stuck in a bounded wait
+        if "s" not in state:
+            torch.cuda.set_device(ps.device)
+            state["s"] = torch.cuda.Stream(device=ps.device)
+        with torch.cuda.stream(state["s"]):
+            f = ps.flag_words()
         return [int(x) for x in f[L.F_HEARTBEAT:L.F_HEARTBEAT + ps.world]]
     return HeartbeatWatchdog(read, ps.world, timeout_s, on_stale=on_stale)

@@ -29,6 +29,8 @@ extern "C" {
 #define DPS_F_TORN_PULLS 35     /* async pulls that stayed inconsistent after retries            */
 #define DPS_F_DROPPED 36        /* async pushes skipped because the owner's ring had no room     */
 #define DPS_F_ALIVE 37          /* sync: mask of source ranks this owner still waits for (set to all W at start) */
+#define DPS_F_UPDATE_NS 40       /* [2] 64-bit: nanoseconds spent in the reduce/apply loops (CTA 0), device-timed */
+#define DPS_F_ROUND 39          /* sync round this owner's reduce last entered (read by the gRPC door) */
 #define DPS_F_PULLEXPECT 38     /* pull deliveries expected so far (accumulated per round: live owners x CTAs)   */
 #define DPS_F_HEARTBEAT 64      /* [32] last step seen from each source rank                     */
 #define DPS_F_RING_TAIL 96      /* async ring: next ticket (peer atomics)                        */
@@ -49,7 +51,9 @@ extern "C" {
 #define DPS_F_DROP 832          /* [32] local: this step's push to owner o was skipped            */
 #define DPS_F_SEGCOUNT 864      /* [16] segmented pull: deliveries received per layer group           */
 #define DPS_F_SEGEXPECT 880     /* [16] segmented pull: deliveries expected so far per layer group    */
-#define DPS_F_JOIN 896          /* [32] first sync round in which extra source x (rank W+x) takes part  */
+#define DPS_F_CONSUMED 896      /* [32] pushes of extra source x (rank W+x) folded into a round so far     */
+#define DPS_F_CONSUMED_ROUND 928 /* [32] round that consumed the latest push of extra source x           */
+#define DPS_F_INCLUDE 960       /* mask of extra sources folded into the CURRENT round (remote_gate_kernel) */
 #define DPS_MAX_SEGS 16
 #define DPS_FLAG_WORDS 1024
 
@@ -121,11 +125,17 @@ int dps_bump_step(const DpsTables* T, void* stream);
 /* reference: server.py:290-304,171-186 (async apply-on-arrival with staleness weighting) */
 int dps_push_async(const DpsTables* T, int rank, unsigned step, int ctas, unsigned long long timeout_ns,
                    void* stream);
+/* policy: 0 reference (version per accepted update, bound as given) | 1 bound widened by W-1 | 2 one version per
+ * drained batch.  bump_step: 1 = this scan closes the rank's own push (same stream); 0 = a dedicated server stream
+ * drives the apply and dps_pull_async(bump_step=1) closes the push instead. */
 int dps_async_apply(const DpsTables* T, int owner, int producer_ctas, int staleness_bound, float alpha,
                     float floor_w, int max_batch, float lr, float momentum, float weight_decay, int ctas,
-                    void* stream);
-int dps_pull_async(const DpsTables* T, int rank, int ctas, void* stream);
+                    int policy, int bump_step, void* stream);
+int dps_pull_async(const DpsTables* T, int rank, int ctas, int bump_step, void* stream);
 int dps_publish(const DpsTables* T, int owner, void* stream);
+/* *word = (*word & and_mask) | or_mask with device atomics (membership commands of the gRPC front door on flag
+ * words that the reduce kernels also update; reference: the registry of server.py:190-211,306-318). */
+int dps_flag_update(uint32_t* word, unsigned and_mask, unsigned or_mask, void* stream);
 
 #ifdef __cplusplus
 }
