@@ -7,9 +7,10 @@ NCCL all-reduce + cuDNN/cuBLAS (bf16 autocast, channels_last, SGD), device-timed
 
 --graph captures the WHOLE step (forward, backward, gradient all-reduce, SGD) in one CUDA graph at any world size, so
 the baseline is not bound by host launch overhead (an eager 8-rank run on one host is: 7.8 ms/step against 4.6 at one
-rank).  With world > 1 the capture first tries real DistributedDataParallel (bucketed all-reduce overlapped with
-backward, built and warmed up on a side stream as the PyTorch CUDA-graph notes require); if that capture is refused
-it falls back to the same math with ONE flat NCCL all-reduce of the gradients after backward ("flat-allreduce").
+rank).  With world > 1 the captured step is cuDNN forward/backward + ONE flat NCCL all-reduce of all gradients + SGD
+("flat-allreduce": the data-parallel math of DDP without its Python-side bucket hooks; `--ddp` tries to capture the real
+DistributedDataParallel wrapper instead, which did not return from capture at 2 ranks on this stack).  Without --graph
+the real DDP wrapper runs eagerly.
 """
 import argparse
 import json
@@ -29,7 +30,8 @@ p.add_argument("--warmup", type=int, default=5)
 p.add_argument("--batch", type=int, default=128)
 p.add_argument("--fp32", action="store_true")
 p.add_argument("--graph", action="store_true", help="capture fwd+bwd+all-reduce+step in one CUDA graph")
-p.add_argument("--flat", action="store_true", help="skip DDP: one flat all-reduce of the gradients after backward")
+p.add_argument("--ddp", action="store_true", help="with --graph: try to capture real DistributedDataParallel (its whole-step "
+               "capture hung on this stack at 2 ranks; default = the same math with one flat NCCL all-reduce in the graph)")
 a = p.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 local = int(os.environ.get("LOCAL_RANK", rank))
@@ -84,7 +86,7 @@ def capture(step):
 
 
 graph, how = None, "eager"
-use_ddp = world > 1 and not a.flat
+use_ddp = world > 1 and a.ddp
 if a.graph:
     side = torch.cuda.Stream()
     try:
@@ -101,6 +103,7 @@ if a.graph:
         graph = capture(step)
         how = "flat-allreduce in one CUDA graph (DDP capture refused)"
 else:
+    use_ddp = world > 1
     step = build(use_ddp)
     how = ("DDP" if use_ddp else "single") + " eager"
     for _ in range(max(3, a.warmup)):

@@ -26,9 +26,11 @@ if mode == "sync":
     # oracle for the FIRST step: mean over ranks of the fp16-rounded local gradients, applied to the initial master
     w0 = job.ps.gather_master().clone()
     job.worker.engine.load_batch(xs[0], ys[0])
-    hook, job.worker.engine.seg_wait = job.worker.engine.seg_wait, None     # oracle pass: compute only, no pull waits
-    job.worker.engine.forward_backward()
-    job.worker.engine.seg_wait = hook
+    eng = job.worker.engine
+    hook, eng.seg_wait = eng.seg_wait, None                 # oracle pass: compute only, no pull waits ...
+    push_hook, eng.on_group_done = eng.on_group_done, None  # ... and no per-group SEND of the overlapped push
+    eng.forward_backward()
+    eng.seg_wait, eng.on_group_done = hook, push_hook
     torch.cuda.synchronize()
     g_local = job.ps.grad[rank].clone().half().float()
     job.ps.grad[rank].zero_()

@@ -41,7 +41,9 @@ __global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(
     const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual, __nv_bfloat16* __restrict__ y,
     float* __restrict__ save_mean, float* __restrict__ save_rstd, float* __restrict__ running_mean,
     float* __restrict__ running_var, long long* __restrict__ num_batches, long long P, int C, int relu,
-    int training, float eps, float momentum) {
+    int training, float eps, float momentum, double inv_sum, double inv_sq) {
+  // inv_sum = 1 / (2^32 P), inv_sq = 1 / (2^24 P), computed on the host: the FP64 pipe of this part is vestigial, and
+  // two double divisions per channel in every CTA's prologue were a measurable share of the small layers' ~4 us
   __shared__ float s_scale[kMaxC], s_shift[kMaxC];
   pdl_launch_dependents();
   pdl_wait();
@@ -65,9 +67,9 @@ __global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(
     float mean, var;
     if (training) {
       // 64-bit fixed point from the conv epilogue: sum x 2^32, sum of squares x 2^24
-      const double m = (double)stats[c] * (1.0 / 4294967296.0) / (double)P;
+      const double m = (double)stats[c] * inv_sum;
       mean = (float)m;
-      var = fmaxf((float)((double)stats[C + c] * (1.0 / 16777216.0) / (double)P - m * m), 0.f);
+      var = fmaxf((float)((double)stats[C + c] * inv_sq - m * m), 0.f);
     } else {
       mean = running_mean[c];
       var = running_var[c];
@@ -265,7 +267,8 @@ DPS_API int dps_bn_forward(const void* x, const long long* stats, const float* g
   if (C % 8 || C > kMaxC || kBnThreads % (C / 8)) DPS_FAIL(1, "bn: unsupported channel count %d", C);
   DPS_CHECK(launch_pdl(bn_fwd_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, (cudaStream_t)stream,
       (const __nv_bfloat16*)x, stats, gamma, beta, (const __nv_bfloat16*)residual, (__nv_bfloat16*)y, save_mean,
-      save_rstd, running_mean, running_var, num_batches, P, C, relu, training, eps, momentum));
+      save_rstd, running_mean, running_var, num_batches, P, C, relu, training, eps, momentum,
+      1.0 / (4294967296.0 * (double)P), 1.0 / (16777216.0 * (double)P)));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }

@@ -1592,6 +1592,16 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     DPS_FAIL(1, "no 128-pixel box divides N=%d H=%d W=%d", N, TH, TW);
   }
   if (any_halo) { pl->cluster = 1; pl->pair = false; }
+  if (pl->cluster > 1) {
+    // TMA multicast loads here read only this GPU's memory, since on B200 a TMA multicast load from another GPU's
+    // memory hung the GPU: the cluster variant (activation box multicast) is only chosen for a buffer that lives on
+    // the current device; anything else (a peer mapping) takes the plain per-CTA loads.
+    cudaPointerAttributes at;
+    int cur = -1;
+    const bool local = cudaGetDevice(&cur) == cudaSuccess && cudaPointerGetAttributes(&at, x) == cudaSuccess &&
+                       at.type == cudaMemoryTypeDevice && at.device == cur;
+    if (!local) { cudaGetLastError(); pl->cluster = 1; }
+  }
   if (pl->halo2) pl->block_n = 64;
   while (pl->cluster > 1 && (kTileM / pl->cluster) % cp.BW != 0) pl->cluster /= 2;   // a slice is whole box lines
   // each CTA of a cluster loads 128/cluster rows of the box: sub-box = BW x sub_bh x sub_bn

@@ -153,6 +153,8 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--local-step-policy", choices=["reference", "accumulate"], default="accumulate")
     p.add_argument("--nonblocking-sync", action="store_true")
     p.add_argument("--barrier-timeout-s", type=float, default=60.0)
+    p.add_argument("--heartbeat-timeout-s", type=float, default=30.0)
+    p.add_argument("--no-watchdog", dest="watchdog", action="store_false")
     p.add_argument("--worker-timeout-s", type=float, default=0.0)
     p.add_argument("--compat-pickle", action="store_true")
     p.add_argument("--compress", choices=["fp16", "none"], default="fp16")
