@@ -28,9 +28,12 @@ namespace dps {
 
 constexpr int VEC = 8;  // elements per thread per iteration (16 B of fp16/bf16, 32 B of fp32)
 
+// local shard offset -> arena offset.  BS is a power of two (check_tables): shift and mask, no 64-bit division in the
+// copy loops.
 __device__ __forceinline__ long long global_index(long long l, int owner, int W, int BS) {
-  long long lb = l / BS;
-  return (lb * W + owner) * (long long)BS + (l - lb * BS);
+  const int sh = __ffs(BS) - 1;
+  const long long lb = l >> sh;
+  return ((lb * W + owner) << sh) + (l & (long long)(BS - 1));
 }
 
 struct F8 {
@@ -136,18 +139,30 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     for (int oo = 0; oo < W; ++oo) {
       const int o = (r + 1 + oo) % W;                        // rotate so owners are hit evenly
       uint16_t* dst = T.stage[o] + (long long)r * E;           // peer-mapped staging slot [src=r]
-      for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
-        const long long g = global_index(l, o, W, BS);
-        F8 v = load_f32x8(grad + g);
-        if (!compress_fp16) {
-          // uncompressed wire (compress = 'none'): fp32 straight into the staging slot, which is allocated twice as
-          // large for this mode (slot stride 2E halfs == E floats)
-          store_f32x8(reinterpret_cast<float*>(T.stage[o]) + (long long)r * E + l, v);
-        } else {
-          st_v4(dst + l, to_f16x8(v));
+      // four independent 32-byte loads per thread before the first store: the loop is bound by load latency otherwise
+      const long long stride = (long long)blockDim.x * VEC;
+      for (long long l0 = lo + threadIdx.x * VEC; l0 < hi; l0 += 4 * stride) {
+        F8 v[4];
+        long long g[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const long long l = l0 + j * stride;
+          if (l < hi) { g[j] = global_index(l, o, W, BS); v[j] = load_f32x8(grad + g[j]); }
         }
-        F8 z = {};                                            // gradients are consumed: zero for next step
-        store_f32x8(grad + g, z);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const long long l = l0 + j * stride;
+          if (l >= hi) break;
+          if (!compress_fp16) {
+            // uncompressed wire (compress = 'none'): fp32 straight into the staging slot, which is allocated twice as
+            // large for this mode (slot stride 2E halfs == E floats)
+            store_f32x8(reinterpret_cast<float*>(T.stage[o]) + (long long)r * E + l, v[j]);
+          } else {
+            st_v4(dst + l, to_f16x8(v[j]));
+          }
+          F8 z = {};                                          // gradients are consumed: zero for next step
+          store_f32x8(grad + g[j], z);
+        }
       }
     }
     // one system-scope fence for all W destinations, then relaxed arrivals (a release per owner would cost a
@@ -291,14 +306,23 @@ __global__ void __launch_bounds__(256) pull_seg_kernel(const __grid_constant__ D
     const long long lo = s0 + (long long)b * per, hi = min(s1, lo + per);
     for (int o = T.rank_lo; o < T.rank_hi; ++o) {
       const float* master = T.master[o];
-      for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
-        const long long g = global_index(l, o, W, BS);
-        const F8 p = load_f32x8(master + l);
-        const uint4 h = to_bf16x8(p);
-        for (int ww = 0; ww < W; ++ww) {
-          const int w = (o + ww) % W;
-          st_v4(T.wbf16[w] + g, h);
-          if (g < n_small) store_f32x8(T.small[w] + g, p);
+      const long long stride = (long long)blockDim.x * VEC;
+      for (long long l0 = lo + threadIdx.x * VEC; l0 < hi; l0 += 4 * stride) {
+        F8 p[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j)
+          if (l0 + j * stride < hi) p[j] = load_f32x8(master + l0 + j * stride);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const long long l = l0 + j * stride;
+          if (l >= hi) break;
+          const long long g = global_index(l, o, W, BS);
+          const uint4 h = to_bf16x8(p[j]);
+          for (int ww = 0; ww < W; ++ww) {
+            const int w = (o + ww) % W;
+            st_v4(T.wbf16[w] + g, h);
+            if (g < n_small) store_f32x8(T.small[w] + g, p[j]);
+          }
         }
       }
       __syncthreads();
@@ -599,7 +623,8 @@ static int check_tables(const DpsTables* T) {
   if (T->world < 1 || T->world > DPS_MAX_RANKS) DPS_FAIL(1, "world %d out of range", T->world);
   if (T->n_extra < 0 || T->world + T->n_extra > DPS_MAX_RANKS) DPS_FAIL(1, "world + extra sources exceeds %d", DPS_MAX_RANKS);
   if (T->rank_lo < 0 || T->rank_hi > T->world + T->n_extra || T->rank_lo >= T->rank_hi) DPS_FAIL(1, "bad rank range");
-  if (T->block_elems <= 0 || T->block_elems % 8 != 0) DPS_FAIL(1, "block_elems must be a positive multiple of 8");
+  if (T->block_elems <= 0 || T->block_elems % 8 != 0 || (T->block_elems & (T->block_elems - 1)))
+    DPS_FAIL(1, "block_elems must be a power of two >= 8");
   if (T->shard_elems <= 0 || T->shard_elems % T->block_elems != 0) DPS_FAIL(1, "shard_elems must be a multiple of block_elems");
   return 0;
 }
