@@ -446,10 +446,11 @@ class ResNetEngine:
         s = torch.cuda.Stream(device=self.dev)
         s.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(s):
-            saved, self.seg_wait = self.seg_wait, None       # the warm-up pass is compute only
-            for _ in range(warmup):
+            saved, self.seg_wait = self.seg_wait, None       # the warm-up pass is compute only: no pull waits ...
+            hook, self.on_group_done = self.on_group_done, None      # ... and no SEND of the overlapped push (it would
+            for _ in range(warmup):                                  # leave the arrival counters ahead of the rounds)
                 self.forward_backward()
-            self.seg_wait = saved
+            self.seg_wait, self.on_group_done = saved, hook
         torch.cuda.current_stream().wait_stream(s)
         torch.cuda.synchronize(self.dev)
         own = (self.images, self.labels)
