@@ -493,8 +493,10 @@ __device__ __forceinline__ void conv_epilogue_rr(const ConvParams& p, int grp, i
 // activation box.  Each CTA fetches 1/CL of its rows and TMA-multicasts them into all CL CTAs (L2->SM activation
 // traffic / CL); the weight tile stays private.  A stage may be refilled only after ALL CL consumers released it:
 // every MMA thread multicasts its tcgen05.commit to the `empty` barrier of all CTAs (barrier count = CL).
-template <int BLOCK_N, bool B_MN, int CL>
-__global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant__ CUtensorMap tmA,
+// EPI = epilogue warps (4, or 8 for one-wave grids: one CTA per SM, so the wider epilogue costs no occupancy and halves
+// the serial tail of the kernel -- TMEM drain, statistics, stores -- that nothing overlaps when a CTA has ONE tile).
+template <int BLOCK_N, bool B_MN, int CL, int EPI = 4>
+__global__ void __launch_bounds__(64 + 32 * EPI) tapconv_kernel(const __grid_constant__ CUtensorMap tmA,
                                                            const __grid_constant__ CUtensorMap tmB,
                                                            const __grid_constant__ ConvParams p) {
   using S = ConvSmem<BLOCK_N>;
@@ -610,7 +612,7 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
     }
   } else {
     // ===================== epilogue (4 warps) =====================
-    conv_epilogue<BLOCK_N, 4>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
+    conv_epilogue<BLOCK_N, EPI>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
   }
 
   tc_fence_before();
@@ -638,8 +640,8 @@ __global__ void __launch_bounds__(kThreads) tapconv_kernel(const __grid_constant
 constexpr int kPairN = 128;
 constexpr int kPairStage = kABytes + 64 * kKBlock * 2;      // 16 KiB activations + 8 KiB half weight tile
 
-template <bool B_MN>
-__global__ void __launch_bounds__(kThreads) pairconv_kernel(const __grid_constant__ CUtensorMap tmA,
+template <bool B_MN, int EPI = 4>
+__global__ void __launch_bounds__(64 + 32 * EPI) pairconv_kernel(const __grid_constant__ CUtensorMap tmA,
                                                             const __grid_constant__ CUtensorMap tmB,
                                                             const __grid_constant__ ConvParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -727,7 +729,7 @@ __global__ void __launch_bounds__(kThreads) pairconv_kernel(const __grid_constan
       umma_commit_2sm(tmem_full, 3);         // accumulators of both CTAs complete
     }
   } else {
-    conv_epilogue<kPairN, 4>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
+    conv_epilogue<kPairN, EPI>(p, grp, n0, h0, w0, c_out0, smem_u32(stages), tmem_base, tmem_full, 0, nullptr);
   }
 
   tc_fence_before();
@@ -1429,6 +1431,7 @@ struct ConvPlan {
   bool halo2;                     // halo2conv_kernel (128 reduction channels, 64-wide resident weight slices)
   int cluster;                    // CTAs per cluster along N (activation multicast); 1 = none
   bool pair;                      // pairconv_kernel (cta_group::2)
+  bool epi8;                      // one-wave grid: 8 epilogue warps
   CUtensorMap tmA, tmB;
   ConvParams cp;
   WgradParams wp;
@@ -1438,31 +1441,31 @@ struct ConvPlan {
   size_t smem;
 };
 
-template <int BN_, bool MN_, int CL_ = 1>
+template <int BN_, bool MN_, int CL_ = 1, int EPI_ = 4>
 static int launch_tapconv(const ConvPlan& pl, cudaStream_t st) {
-  auto kern = tapconv_kernel<BN_, MN_, CL_>;
+  auto kern = tapconv_kernel<BN_, MN_, CL_, EPI_>;
   static bool configured = false;
   if (!configured) {
     DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                    ConvSmem<BN_>::total(kMaxStages)));
     configured = true;
   }
-  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(kThreads), ConvSmem<BN_>::total(pl.cp.nstages), st, dim3(1, CL_, 1),
-                               pl.tmA, pl.tmB, pl.cp));
+  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(64 + 32 * EPI_), ConvSmem<BN_>::total(pl.cp.nstages), st,
+                               dim3(1, CL_, 1), pl.tmA, pl.tmB, pl.cp));
   DPS_CHECK(cudaGetLastError());
   return 0;
 }
 
-template <bool MN_>
+template <bool MN_, int EPI_ = 4>
 static int launch_pair(const ConvPlan& pl, cudaStream_t st) {
-  auto kern = pairconv_kernel<MN_>;
+  auto kern = pairconv_kernel<MN_, EPI_>;
   static bool configured = false;
   const int smem_max = 1024 + kMaxStages * kPairStage + kCtrlBytes;
   if (!configured) {
     DPS_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_max));
     configured = true;
   }
-  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(kThreads), 1024 + pl.cp.nstages * kPairStage + kCtrlBytes, st,
+  DPS_CHECK(launch_pdl_cluster(kern, pl.grid, dim3(64 + 32 * EPI_), 1024 + pl.cp.nstages * kPairStage + kCtrlBytes, st,
                                dim3(2, 1, 1), pl.tmA, pl.tmB, pl.cp));
   return 0;
 }
@@ -1688,6 +1691,10 @@ DPS_API int dps_conv_plan_create(int kind, const void* x, const void* w, void* o
     const long long ctas = (long long)pl->grid.x * pl->grid.y * pl->grid.z;
     cp.nstages = ctas <= 148 ? (one_wave_stages < 4 ? 4 : one_wave_stages) : 4;          // staging needs >= 3 stages of 24 KiB
   }
+  {
+    const char* e = getenv("DPS_EPI8");
+    pl->epi8 = !(e && e[0] == '0') && cp.nstages == kMaxStages && pl->cluster == 1;
+  }
   if (pl->halo) {
     cp.tiles_total = cp.tiles_w * cp.tiles_h * tiles_n;
     pl->grid = dim3(cp.tiles_total < 148 ? cp.tiles_total : 148, 1, 1);      // persistent: one CTA per SM
@@ -1826,11 +1833,16 @@ DPS_API int dps_conv_plan_run(void* plan, void* stream) {
   if (pl->kind == 2) return pl->block_n == 128 ? launch_wgrad<128>(*pl, st) : launch_wgrad<64>(*pl, st);
   if (pl->halo) return pl->b_mn ? launch_halo<true>(*pl, st) : launch_halo<false>(*pl, st);
   if (pl->halo2) return pl->b_mn ? launch_halo2<true>(*pl, st) : launch_halo2<false>(*pl, st);
+  if (pl->pair && pl->epi8) return pl->b_mn ? launch_pair<true, 8>(*pl, st) : launch_pair<false, 8>(*pl, st);
   if (pl->pair) return pl->b_mn ? launch_pair<true>(*pl, st) : launch_pair<false>(*pl, st);
   if (pl->block_n == 64 && pl->cluster == 4)
     return pl->b_mn ? launch_tapconv<64, true, 4>(*pl, st) : launch_tapconv<64, false, 4>(*pl, st);
   if (pl->block_n == 64 && pl->cluster == 2)
     return pl->b_mn ? launch_tapconv<64, true, 2>(*pl, st) : launch_tapconv<64, false, 2>(*pl, st);
+  if (pl->epi8 && pl->cluster == 1) {
+    if (pl->b_mn) return pl->block_n == 128 ? launch_tapconv<128, true, 1, 8>(*pl, st) : launch_tapconv<64, true, 1, 8>(*pl, st);
+    return pl->block_n == 128 ? launch_tapconv<128, false, 1, 8>(*pl, st) : launch_tapconv<64, false, 1, 8>(*pl, st);
+  }
   if (pl->b_mn) return pl->block_n == 128 ? launch_tapconv<128, true>(*pl, st) : launch_tapconv<64, true>(*pl, st);
   return pl->block_n == 128 ? launch_tapconv<128, false>(*pl, st) : launch_tapconv<64, false>(*pl, st);
 }
