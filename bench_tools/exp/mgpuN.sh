@@ -10,5 +10,4 @@ $TR --nproc-per-node $N --master-port 29813 bench_tools/pushpull_sweep.py --out 
 $TR --nproc-per-node $N --master-port 29814 bench_tools/ddp_baseline.py --graph --steps 100 > gpurun_out/mgpu/ddp_${N}gpu.json 2> gpurun_out/mgpu/ddp_${N}gpu.err; cat gpurun_out/mgpu/ddp_${N}gpu.json; tail -2 gpurun_out/mgpu/ddp_${N}gpu.err
 if [ "$N" = "8" ]; then
   timeout 120 python bench.py --gpus 1 --steps 200 --warmup 10 > gpurun_out/mgpu/bench_1gpu_sync_samebox.json 2>/dev/null; cut -c1-200 gpurun_out/mgpu/bench_1gpu_sync_samebox.json
-  $TR --nproc-per-node 8 --master-port 29815 bench.py --gpus 8 --steps 200 --warmup 10 --mode async --staleness-policy world > gpurun_out/mgpu/bench_8gpu_async_world.json 2>/dev/null; cut -c1-330 gpurun_out/mgpu/bench_8gpu_async_world.json
 fi

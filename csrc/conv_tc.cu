@@ -18,10 +18,11 @@
 //      epilogue: tcgen05.ld -> bf16 -> smem staging -> coalesced stores; optional fused residual-gradient
 //              add (`addend`), optional fused per-channel sum / sum-of-squares for the following BatchNorm.
 //
-//  wgrad_kernel    dW[co, tap, ci] += sum over pixels dY[pix, co] * X_tap[pix, ci]
-//      both operands are pixel-major in memory == MN-major UMMA operands straight from TMA boxes;
-//      up to 4 taps x 128 ci of fp32 accumulators live in TMEM (512 columns); split over pixel ranges
-//      across CTAs, reduced with coalesced fp32 red.global.add into the flat gradient arena.
+//  wgrad_kernel    dW[co, tap, ci] += sum over pixels X_tap[pix, ci] * dY[pix, co]
+//      both operands are pixel-major in memory == MN-major UMMA operands straight from TMA boxes; the activation
+//      tap is the M operand, so accumulator rows are ci and a warp's registers reduce into dW with coalesced fp32
+//      red.global.add (no transpose); up to 4 taps x 128 co of fp32 accumulators live in TMEM (512 columns);
+//      split over pixel ranges across CTAs.
 //
 // Warp roles (192 threads): warp 0 = TMA producer, warp 1 = TMEM owner + single-thread MMA issuer,
 // warps 2..5 = epilogue (TMEM lane quadrant = warp_id % 4).
@@ -1135,23 +1136,28 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
     }
   } else if (warp == 1) {
     if (elect_one()) {
-      constexpr uint32_t idesc = make_idesc_bf16(128, NB, 1, 1);       // both operands MN-major
+      // D[(ci)][co] = X_tap^T * dY: the activation tap is the M operand (rows = ci; with 64 input channels rows
+      // 64..127 alias rows 0..63 through LBO = 0), dY the N operand.  Rows of the accumulator are then ci, so a warp's
+      // 32 lanes hold 32 consecutive ci of one co and the split-K reduction is a coalesced fp32 red.global.add straight
+      // from registers (no shared-memory transpose, no block barriers in the epilogue) -- the scheme of wgrad_halo_kernel.
+      const int nco = p.co_alias ? 64 : 128;                           // accumulator columns per tap
+      const uint32_t idesc = p.co_alias ? make_idesc_bf16(128, 64, 1, 1) : make_idesc_bf16(128, 128, 1, 1);
       const uint32_t stage0 = smem_u32(stages);
       const uint32_t stage_bytes = (uint32_t)p.stage_bytes;
-      const uint64_t adesc0 = make_smem_desc(stage0, p.co_alias ? 0 : dy_atom_bytes, 1024);
-      const uint64_t bdesc0 = make_smem_desc(stage0 + S::kDyBytes, 8192, 1024);
+      const uint64_t adesc0 = make_smem_desc(stage0 + S::kDyBytes, NB == 128 ? 8192 : 0, 1024);     // X tap
+      const uint64_t bdesc0 = make_smem_desc(stage0, dy_atom_bytes, 1024);                          // dY
       int s = 0;
       uint32_t ph = 0;
       for (int i = 0; i < nkb; ++i) {
         mbar_wait(&full[s], ph);
         tc_fence_after();
         const uint64_t soff = (uint64_t)((s * stage_bytes) >> 4);
-        const uint64_t adesc = adesc0 + soff;
+        const uint64_t bdesc = bdesc0 + soff;
         for (int tp = 0; tp < ntaps; ++tp) {
-          const uint64_t bdesc = bdesc0 + soff + (uint64_t)((tp * S::kXBytes) >> 4);
+          const uint64_t adesc = adesc0 + soff + (uint64_t)((tp * S::kXBytes) >> 4);
 #pragma unroll
           for (int k = 0; k < 4; ++k)          // 64 pixels = 4 x UMMA_K(16); +16 rows of 128 B per step
-            umma_bf16(tmem_base + tp * NB, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc,
+            umma_bf16(tmem_base + tp * nco, adesc + (uint64_t)(k * 128), bdesc + (uint64_t)(k * 128), idesc,
                       (i | k) != 0 ? 1u : 0u);
         }
         umma_commit(&empty[s]);
@@ -1162,33 +1168,25 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
   } else {
     const int q = warp & 3;
     const int lane = lane_id();
-    const int et = threadIdx.x - 64;
-    float* stage = reinterpret_cast<float*>(stages);      // [128 co][33] fp32 transpose buffer (16.5 KiB)
-    if (nkb > 0) {
+    if (nkb > 0 && q * 32 < NB) {                          // NB == 64: accumulator rows 64..127 are aliases
       mbar_wait(tmem_full, 0);
       tc_fence_after();
-      const int co_rows = p.co_alias ? 64 : min(128, p.Cout - cot * 128);
+      const int nco = p.co_alias ? 64 : 128;
+      const int ci = q * 32 + lane;
+      const bool row_ok = cic * NB + ci < p.valid_cols;    // stem: only 27 of the 64 padded columns exist in dW
       for (int tp = 0; tp < ntaps; ++tp) {
-        const int col_base = p.taps[tg][tp].k_off + cic * NB;          // dW column of this tap / ci chunk
-        for (int c = 0; c < NB / 32; ++c) {
+        float* dst = p.dw + (size_t)(cot * 128) * p.dw_pitch + p.taps[tg][tp].k_off + cic * NB + ci;
+        for (int c = 0; c < nco / 32; ++c) {
           uint32_t r[32];
-          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tp * NB + c * 32, r);
+          tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tp * nco + c * 32, r);
           tmem_ld_wait();
-          const int row = q * 32 + lane;
+          if (row_ok) {
 #pragma unroll
-          for (int j = 0; j < 32; ++j) stage[row * 33 + j] = __uint_as_float(r[j]);
-          asm volatile("bar.sync 1, 128;" ::: "memory");
-          // coalesced reduction into dW: one warp instruction covers 32 consecutive ci of one co row
-          const int ci = c * 32 + lane;
-          if (ci < p.valid_cols - cic * NB) {
-            for (int rr = q; rr < co_rows; rr += 4)
-              atomicAdd(p.dw + (size_t)(cot * 128 + rr) * p.dw_pitch + col_base + ci, stage[rr * 33 + lane]);
+            for (int j = 0; j < 32; ++j) atomicAdd(dst + (size_t)(c * 32 + j) * p.dw_pitch, __uint_as_float(r[j]));
           }
-          asm volatile("bar.sync 1, 128;" ::: "memory");
         }
       }
     }
-    (void)et;
   }
 
   tc_fence_before();
@@ -1758,7 +1756,8 @@ DPS_API int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int 
   wp.ci_chunks = Cin / NB;
   wp.Cout = Cout; wp.dw_pitch = dw_pitch; wp.dw = dw;
   wp.valid_cols = valid_cols;
-  const int max_taps = 512 / NB;
+  const int nco = (Cout == 64) ? 64 : 128;                    // accumulator columns per tap (TMEM: 512 in all)
+  const int max_taps = (512 / nco) < (512 / NB) ? (512 / nco) : (512 / NB);
   const int total_taps = R * R;
   // balanced tap groups
   const int ngroups = (total_taps + max_taps - 1) / max_taps;
