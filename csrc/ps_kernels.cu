@@ -418,12 +418,21 @@ __global__ void __launch_bounds__(256) push_async_kernel(const __grid_constant__
   const uint32_t slot = ticket % (uint32_t)R;
   uint16_t* dst = T.ring[o] + (long long)slot * E;
   float* grad = T.grad[r];
-  for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
-    const long long g = global_index(l, o, W, BS);
-    F8 v = load_f32x8(grad + g);
-    st_v4(dst + l, to_f16x8(v));
-    F8 z = {};
-    store_f32x8(grad + g, z);
+  const long long stride = (long long)blockDim.x * VEC;
+  for (long long l0 = lo + threadIdx.x * VEC; l0 < hi; l0 += 4 * stride) {     // four loads in flight per thread
+    F8 v[4];
+    long long g[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j)
+      if (l0 + j * stride < hi) { g[j] = global_index(l0 + j * stride, o, W, BS); v[j] = load_f32x8(grad + g[j]); }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const long long l = l0 + j * stride;
+      if (l >= hi) break;
+      st_v4(dst + l, to_f16x8(v[j]));
+      F8 z = {};
+      store_f32x8(grad + g[j], z);
+    }
   }
   __syncthreads();
   if (threadIdx.x == 0) {
@@ -573,10 +582,22 @@ __global__ void __launch_bounds__(256) pull_async_kernel(const __grid_constant__
       s_ver = ld_acquire_sys(of + DPS_F_VERSION);
     }
     __syncthreads();
-    for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
-      const long long g = global_index(l, o, W, BS);
-      st_v4(T.wbf16[r] + g, ld_v4(T.pub[o] + l));
-      if (g < n_small) store_f32x8(T.small[r] + g, load_f32x8(T.pubsmall[o] + g));
+    // peer LOADS over NVLink have ~2 us of latency: eight 16-byte loads per thread in flight before the first store
+    // (one at a time, the 22 MB gather cost ~90 us at 4 GPUs -- most of the async step's gap to the sync step)
+    const long long stride = (long long)blockDim.x * VEC;
+    for (long long l0 = lo + threadIdx.x * VEC; l0 < hi; l0 += 8 * stride) {
+      uint4 v[8];
+#pragma unroll
+      for (int j = 0; j < 8; ++j)
+        if (l0 + j * stride < hi) v[j] = ld_v4(T.pub[o] + l0 + j * stride);
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const long long l = l0 + j * stride;
+        if (l >= hi) break;
+        const long long g = global_index(l, o, W, BS);
+        st_v4(T.wbf16[r] + g, v[j]);
+        if (g < n_small) store_f32x8(T.small[r] + g, load_f32x8(T.pubsmall[o] + g));
+      }
     }
     __syncthreads();
     if (threadIdx.x == 0) {

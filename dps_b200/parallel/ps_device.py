@@ -45,6 +45,7 @@ class DevicePS:
         self.is_async = cfg.mode == "async"
         self.ctas = _default_ctas(self.E)
         self.async_ctas = max(1, min(self.ctas, 128 // world))
+        self.pull_async_ctas = max(1, min(self.ctas, 592 // world))     # the gather has no cross-CTA waits: fill the SMs
         self.timeout_ns = int((timeout_s if timeout_s is not None else cfg.barrier_timeout_s) * 1e9)
         # remote workers attached through the gRPC front door are extra SOURCES of the sync push: they get a staging
         # slot on every owner after the W on-box workers, and the master shards move into the peer-visible arena so
@@ -315,7 +316,7 @@ class DevicePS:
     # ------------------------------------------------------------------ async
     def pull_async(self, rank: Optional[int] = None, stream=None, bump_step: bool = False) -> None:
         r = self.rank if rank is None else rank
-        L.check(self.lib.dps_pull_async(self._tp, r, self.async_ctas, int(bump_step), L.stream_ptr(stream)),
+        L.check(self.lib.dps_pull_async(self._tp, r, self.pull_async_ctas, int(bump_step), L.stream_ptr(stream)),
                 "pull_async")
         self.launches += 1
 

@@ -207,3 +207,36 @@ def test_halo2_layer2_kernels(monkeypatch, Nb):
     got = sums.double() / 2 ** 40
     assert torch.allclose(got[:C].float(), dzf.sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
     assert torch.allclose(got[C:].float(), (dzf * xhat).sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
+
+
+@pytest.mark.parametrize("shape", SHAPES, ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_all_passes_at_the_training_batch(shape):
+    """The whole shape matrix again at N = 128, the batch the engine runs: other grids (several waves, CTA pairs on the
+    layer-4 shapes, split reductions with many CTAs per output tile in wgrad) than at N = 8."""
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    Nb = 128
+    g = torch.Generator(device="cuda").manual_seed(11)
+    x = torch.randn(Nb, H, H, Cin, device="cuda", generator=g).to(torch.bfloat16)
+    w = (torch.randn(Cout, R, R, Cin, device="cuda", generator=g) / (R * R * Cin) ** 0.5).to(torch.bfloat16)
+    Ho = H // stride
+    dy = torch.randn(Nb, Ho, Ho, Cout, device="cuda", generator=g).to(torch.bfloat16)
+    y_ref, dx_ref, dw_ref = _ref(x, w, dy, R, stride)
+    kw = dict(N=Nb, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=stride)
+    out = torch.zeros(Nb, Ho, Ho, Cout, device="cuda", dtype=torch.bfloat16)
+    ConvPlan.fprop(x, w, out, **kw).run()
+    dw = torch.zeros(Cout, R, R, Cin, device="cuda")
+    ConvPlan.wgrad(x, dy, dw, **kw).run()
+    if R == 1 and stride == 2:
+        base = torch.randn(Nb, H, H, Cin, device="cuda", generator=g).to(torch.bfloat16)
+        dx = base.clone()
+        ConvPlan.dgrad(dy, w, dx, addend=dx, **kw).run()
+        dx_want = base.float() + dx_ref
+    else:
+        dx = torch.zeros(Nb, H, H, Cin, device="cuda", dtype=torch.bfloat16)
+        ConvPlan.dgrad(dy, w, dx, **kw).run()
+        dx_want = dx_ref
+    torch.cuda.synchronize()
+    assert _relerr(out, y_ref) < 1.5e-2, ("fprop", _relerr(out, y_ref))
+    assert _relerr(dx, dx_want) < 2e-2, ("dgrad", _relerr(dx, dx_want))
+    assert _relerr(dw, dw_ref) < 5e-3, ("wgrad", _relerr(dw, dw_ref))
