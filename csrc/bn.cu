@@ -67,9 +67,10 @@ __global__ void __launch_bounds__(kBnThreads, 3) bn_fwd_kernel(
     float mean, var;
     if (training) {
       // 64-bit fixed point from the conv epilogue: sum x 2^32, sum of squares x 2^24
-      const double m = (double)stats[c] * inv_sum;
-      mean = (float)m;
-      var = fmaxf((float)((double)stats[C + c] * inv_sq - m * m), 0.f);
+      // fp32 from here on (the fixed-point SUMS are exact; E[x^2] - mean^2 in fp32 loses ~6e-8 * (1 + mean^2 / var)
+      // relative precision, far below bf16 activations) -- no FP64 instruction in any CTA's prologue
+      mean = __ll2float_rn(stats[c]) * (float)inv_sum;
+      var = fmaxf(__ll2float_rn(stats[C + c]) * (float)inv_sq - mean * mean, 0.f);
     } else {
       mean = running_mean[c];
       var = running_var[c];
@@ -209,8 +210,8 @@ __global__ void __launch_bounds__(kBnThreads, 3) bn_bwd_apply_kernel(
   }
   const float invP = 1.f / (float)P;
   for (int c = threadIdx.x; c < C; c += blockDim.x) {
-    const float sdz = (float)((double)sums[c] * (1.0 / kGradSumScale));
-    const float sdzx = (float)((double)sums[C + c] * (1.0 / kGradSumScale));
+    const float sdz = __ll2float_rn(sums[c]) * (float)(1.0 / kGradSumScale);
+    const float sdzx = __ll2float_rn(sums[C + c]) * (float)(1.0 / kGradSumScale);
     const float gr = gamma[c] * rstd[c];
     // dx = gr * (dz - sdz/P - xhat * sdzx/P),  xhat = (x - mean) * rstd
     const float k = gr * rstd[c] * sdzx * invP;

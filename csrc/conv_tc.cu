@@ -1045,8 +1045,10 @@ struct WgradSmem {
   static constexpr int total(int nst, int stage_bytes) { return 1024 + nst * stage_bytes + kCtrlBytes; }
 };
 
+constexpr int kWgradThreads = 64 + 32 * 8;     // TMA warp, MMA warp, EIGHT reduction warps (one CTA per SM: 512 TMEM columns)
+
 template <int NB>
-__global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
+__global__ void __launch_bounds__(kWgradThreads) wgrad_kernel(const __grid_constant__ CUtensorMap tmDy,
                                                          const __grid_constant__ CUtensorMap tmX,
                                                          const __grid_constant__ WgradParams p) {
   using S = WgradSmem<NB>;
@@ -1174,9 +1176,10 @@ __global__ void __launch_bounds__(kThreads) wgrad_kernel(const __grid_constant__
       const int nco = p.co_alias ? 64 : 128;
       const int ci = q * 32 + lane;
       const bool row_ok = cic * NB + ci < p.valid_cols;    // stem: only 27 of the 64 padded columns exist in dW
+      const int half = (warp - 2) >> 2;                    // warps 2..5 take the even 32-column chunks, 6..9 the odd ones
       for (int tp = 0; tp < ntaps; ++tp) {
         float* dst = p.dw + (size_t)(cot * 128) * p.dw_pitch + p.taps[tg][tp].k_off + cic * NB + ci;
-        for (int c = 0; c < nco / 32; ++c) {
+        for (int c = half; c < nco / 32; c += 2) {
           uint32_t r[32];
           tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + tp * nco + c * 32, r);
           tmem_ld_wait();
@@ -1224,7 +1227,7 @@ constexpr int kWhXBytes = 100 * 128;                   // 10 x 10 halo pixels x 
 constexpr int kWhStage = kWhDyBytes + 13312;           // X slot rounded up to 1024
 constexpr int kWhMaxStages = 8;
 
-__global__ void __launch_bounds__(kThreads) wgrad_halo_kernel(const __grid_constant__ CUtensorMap tmDy,
+__global__ void __launch_bounds__(kWgradThreads) wgrad_halo_kernel(const __grid_constant__ CUtensorMap tmDy,
                                                               const __grid_constant__ CUtensorMap tmX,
                                                               const __grid_constant__ WgradHaloParams p) {
   extern __shared__ uint8_t smem_raw[];
@@ -1319,8 +1322,8 @@ __global__ void __launch_bounds__(kThreads) wgrad_halo_kernel(const __grid_const
       const int tap = 2 * pr + (q >> 1);
       if (tap > 8) continue;                                  // second half of the padded fifth pair
       float* dst = p.dw + (size_t)(cot * 64) * p.dw_pitch + tap * p.Cin + cic * 64 + ci;
-#pragma unroll
-      for (int c = 0; c < 2; ++c) {
+      {
+        const int c = (warp - 2) >> 2;                        // eight reduction warps: 2..5 -> columns 0..31, 6..9 -> 32..63
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + ((uint32_t)(q * 32) << 16) + pr * 64 + c * 32, r);
         tmem_ld_wait();
@@ -1499,8 +1502,8 @@ static int launch_wgrad_halo(const ConvPlan& pl, cudaStream_t st) {
     DPS_CHECK(cudaFuncSetAttribute(wgrad_halo_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
     configured = true;
   }
-  DPS_CHECK(launch_pdl(wgrad_halo_kernel, pl.grid, dim3(kThreads), 1024 + pl.whp.nstages * kWhStage + 256, st, pl.tmA,
-                       pl.tmB, pl.whp));
+  DPS_CHECK(launch_pdl(wgrad_halo_kernel, pl.grid, dim3(kWgradThreads), 1024 + pl.whp.nstages * kWhStage + 256, st,
+                       pl.tmA, pl.tmB, pl.whp));
   return 0;
 }
 
@@ -1513,7 +1516,7 @@ static int launch_wgrad(const ConvPlan& pl, cudaStream_t st) {
                                    WgradSmem<NB_>::total(1, WgradSmem<NB_>::kBudget)));
     configured = true;
   }
-  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kThreads), WgradSmem<NB_>::total(pl.wp.nstages, pl.wp.stage_bytes), st,
+  DPS_CHECK(launch_pdl(kern, pl.grid, dim3(kWgradThreads), WgradSmem<NB_>::total(pl.wp.nstages, pl.wp.stage_bytes), st,
                        pl.tmA, pl.tmB, pl.wp));
   DPS_CHECK(cudaGetLastError());
   return 0;

@@ -45,7 +45,10 @@ class DevicePS:
         self.is_async = cfg.mode == "async"
         self.ctas = _default_ctas(self.E)
         self.async_ctas = max(1, min(self.ctas, 128 // world))
-        self.pull_async_ctas = max(1, min(self.ctas, 592 // world))     # the gather has no cross-CTA waits: fill the SMs
+        # The gather may have to wait for an owner's apply to finish (seq-lock): it must never fill the SMs, or the
+        # apply it waits for could not be scheduled beside it (measured: 592 CTAs at W = 1 spun out their bound and
+        # counted torn pulls).  256 CTAs in all = fewer than two per SM.
+        self.pull_async_ctas = max(1, min(self.ctas, 256 // world))
         self.timeout_ns = int((timeout_s if timeout_s is not None else cfg.barrier_timeout_s) * 1e9)
         # remote workers attached through the gRPC front door are extra SOURCES of the sync push: they get a staging
         # slot on every owner after the W on-box workers, and the master shards move into the peer-visible arena so
