@@ -416,6 +416,8 @@ class Worker:
         stream, overlapping the previous step), device tensors, or pageable host tensors.  The returned handle is
         valid until two further steps have been issued (its pinned slot is then reused)."""
         use_graph = self.cfg.use_cuda_graph and self.engine_kind == "native"
+        if self.async_server and self.ps._server is None:
+            self.ps.start_async_server()                 # drain() stopped it: training goes on, so does the owner role
         if use_graph and self.graph is None:
             self._build_graph()
         fused_exchange = use_graph and self.cfg.sync_steps == 1
