@@ -17,7 +17,7 @@ a running job (``Config.serve_port``), same proto, same payload codecs, and ever
                    workers never wait for a remote one (a CPU worker needs seconds per step), its gradient is
                    folded into whichever round is current.  For the remote worker the push is a true barrier: the
                    reply is sent when every shard has applied the round that consumed its gradient.
-  JobFinished      detaches the source (owners polling for it notice at once).
+  JobFinished      detaches the source (its membership bit is cleared on every owner).
 """
 from __future__ import annotations
 
@@ -34,7 +34,6 @@ from ..ops import _lib as L
 from . import codec, proto
 
 
-
 class DeviceStoreServicer(proto.ParameterServerServicer):
     def __init__(self, job, verbose: bool = False):
         self.job, self.ps, self.cfg = job, job.ps, job.cfg
@@ -43,7 +42,7 @@ class DeviceStoreServicer(proto.ParameterServerServicer):
                              "FetchParameters only (remote_slots must be 0)")
         self.verbose = verbose
         self.lock = threading.Lock()
-        self.slots: Dict[int, dict] = {}                       # x -> {ip, join, pushes, registered_at, last_seen}
+        self.slots: Dict[int, dict] = {}                       # x -> {ip, pushes, registered_at, last_seen}
         self.stream = torch.cuda.Stream(device=job.device)     # door traffic never sits on the training stream
         self.gradients_processed = 0
         self.rejected = 0
@@ -61,12 +60,6 @@ class DeviceStoreServicer(proto.ParameterServerServicer):
 
     def _versions(self) -> List[int]:
         return [int(self.ps.peer_flags(r)[L.F_VERSION]) for r in range(self.ps.world)]
-
-    def _device_round(self) -> int:
-        """Round this rank's device is executing (the captured step reads and bumps this counter itself)."""
-        if self.ps.device_counters:
-            return int(self.ps.step_ctr[0])
-        return int(self.ps.step)
 
     @property
     def arrivals(self) -> int:
