@@ -76,6 +76,8 @@ struct ConvParams {
   const __nv_bfloat16* fuse_x;
   const float* fuse_mean;
   const float* fuse_rstd;
+  const float* fuse_gamma;        // optional (with fuse_beta): that BN has NO residual input, so its ReLU mask is recomputed
+  const float* fuse_beta;         // from x -- y = relu(x*sc + sh) -- and y is not read at all (a quarter of the epilogue's loads)
   long long* fuse_sums;
   int addend_compact;             // addend is indexed at tile resolution (stride-2 dgrad + 1x1 shortcut gradient)
   long long* stats;               // optional [2*out_C]: per-channel sum (x 2^32) and sum of squares (x 2^24) in
@@ -124,7 +126,7 @@ __device__ __forceinline__ void red_fixed(long long* dst, float v, float scale) 
 // persistent kernels run two such groups side by side, one per TMEM accumulator):
 // TMEM accumulator -> bf16 staging tile -> (BN statistics | addend + fused BN-backward reduction) -> coalesced stores.
 // Warp w may only read TMEM lanes of quadrant (w & 3); with 8 warps each quadrant is split in two column halves.
-template <int BLOCK_N, int EPI_WARPS, int MAX_GROUP = 4>
+template <int BLOCK_N, int EPI_WARPS, int MAX_GROUP = 4, bool MASK_X = true>
 __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int n0, int h0, int w0, int c_out0,
                                               uint32_t stage, uint32_t tmem_acc, uint64_t* tmem_full,
                                               uint32_t full_parity, uint64_t* tmem_empty, int et0 = 64, int bar_id = 1) {
@@ -147,6 +149,7 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
   const uint32_t part_s = stage + 2 * kTileM * kPitch;  // [kParts][4][kPairs] fp32 partials
   const int chunk = et % kChunks, row0 = et / kChunks;
   const bool fuse = p.fuse_y != nullptr;
+  const bool mask_from_x = MASK_X && fuse && p.fuse_gamma != nullptr;   // (compiled out of the register-tight halo kernel)
   const bool use_addend = p.addend != nullptr && (!p.addend_compact || (p.oph[grp] == 0 && p.opw[grp] == 0));
   // box dims are powers of two: shifts instead of divisions
   const int bw_sh = p.bw_sh, bhw_sh = p.bhw_sh, bw_m = (1 << bw_sh) - 1, bhw_m = (1 << bhw_sh) - 1;
@@ -172,12 +175,22 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
       if (use_addend) aa[j] = ld_nc_v4(p.addend + addend_off(rr));
       if (fuse) {
         const size_t off = out_off(rr);
-        ya[j] = ld_nc_v4(p.fuse_y + off);
+        if (!mask_from_x) ya[j] = ld_nc_v4(p.fuse_y + off);
         xa[j] = ld_nc_v4(p.fuse_x + off);
       }
     }
   };
   if (use_addend || fuse) issue(0);
+  // scale / shift of the fused BN for this thread's 8 channels, exactly as bn_fwd_kernel forms them
+  float msc[8], msh[8];
+  if (mask_from_x) {
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int c = c_out0 + chunk * 8 + i;
+      msc[i] = p.fuse_gamma[c] * p.fuse_rstd[c];
+      msh[i] = p.fuse_beta[c] - p.fuse_mean[c] * msc[i];
+    }
+  }
   mbar_wait(tmem_full, full_parity);
   tc_fence_after();
   if constexpr (kColsPerWarp >= 32) {
@@ -267,14 +280,25 @@ __device__ __forceinline__ void conv_epilogue(const ConvParams& p, int grp, int 
         x = unpack_bf16x2(v.w); y = unpack_bf16x2(a.w); v.w = pack_bf16x2(x.x + y.x, x.y + y.y);
       }
       if (fuse) {
-        const uint4 yv = ya[j];
-        // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
-        auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
-          const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
-          const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
-          return gg & (lo | hi);
-        };
-        v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
+        if (mask_from_x) {
+          // y = relu(x * sc + sh) > 0  <=>  x * sc + sh > 0: the forward output is not read
+          auto maskx = [&](uint32_t gg, uint32_t xx, int i) -> uint32_t {
+            const float2 xf = unpack_bf16x2(xx);
+            const uint32_t lo = fmaf(xf.x, msc[i], msh[i]) > 0.f ? 0x0000FFFFu : 0u;
+            const uint32_t hi = fmaf(xf.y, msc[i + 1], msh[i + 1]) > 0.f ? 0xFFFF0000u : 0u;
+            return gg & (lo | hi);
+          };
+          v.x = maskx(v.x, xa[j].x, 0); v.y = maskx(v.y, xa[j].y, 2); v.z = maskx(v.z, xa[j].z, 4); v.w = maskx(v.w, xa[j].w, 6);
+        } else {
+          const uint4 yv = ya[j];
+          // ReLU mask per bf16 lane: y > 0  <=>  sign bit clear and magnitude non-zero
+          auto mask2 = [](uint32_t gg, uint32_t yy) -> uint32_t {
+            const uint32_t lo = ((yy & 0x8000u) == 0u && (yy & 0x7FFFu) != 0u) ? 0x0000FFFFu : 0u;
+            const uint32_t hi = ((yy & 0x80000000u) == 0u && (yy & 0x7FFF0000u) != 0u) ? 0xFFFF0000u : 0u;
+            return gg & (lo | hi);
+          };
+          v.x = mask2(v.x, yv.x); v.y = mask2(v.y, yv.y); v.z = mask2(v.z, yv.z); v.w = mask2(v.w, yv.w);
+        }
         sts_v4(stage + rr * kPitch + chunk * 16, v);       // dz, for the reduction below
         sts_v4(stage_x + rr * kPitch + chunk * 16, xa[j]);
       }
@@ -874,7 +898,7 @@ __global__ void __launch_bounds__(kHaloThreads, 1) haloconv_kernel(const __grid_
     for (int t = blockIdx.x + g * gridDim.x; t < p.tiles_total; t += 2 * gridDim.x, i += 2) {
       const int n = t / tiles_per_img, r = t % tiles_per_img;
       const int h0 = (r / p.tiles_w) * kHaloH, w0 = (r % p.tiles_w) * kHaloW;
-      conv_epilogue<64, kHaloGroupWarps, 2>(p, 0, n, h0, w0, 0, my_staging, tmem_base + g * 64, &tfull[g], (i >> 1) & 1,
+      conv_epilogue<64, kHaloGroupWarps, 2, false>(p, 0, n, h0, w0, 0, my_staging, tmem_base + g * 64, &tfull[g], (i >> 1) & 1,
                                          &tempty[g], 64 + g * 32 * kHaloGroupWarps, 1 + g);
     }
   }
@@ -1816,6 +1840,18 @@ DPS_API int dps_conv_plan_fuse_bn_bwd(void* plan, const void* y, const void* x, 
   pl->cp.fuse_mean = mean;
   pl->cp.fuse_rstd = rstd;
   pl->cp.fuse_sums = sums;
+  pl->cp.fuse_gamma = pl->cp.fuse_beta = nullptr;
+  return 0;
+}
+
+// The fused BatchNorm has no residual input and is followed by ReLU: its mask can be recomputed from x
+// (y = relu(x * gamma*rstd + beta - mean*gamma*rstd)), so the epilogue stops reading y.
+DPS_API int dps_conv_plan_fuse_bn_mask_from_x(void* plan, const float* gamma, const float* beta) {
+  ConvPlan* pl = reinterpret_cast<ConvPlan*>(plan);
+  if (pl->kind != 1 || pl->cp.fuse_y == nullptr) DPS_FAIL(1, "fuse_bn_mask_from_x: call dps_conv_plan_fuse_bn_bwd first");
+  if (pl->halo2 || pl->halo) return 0;             // those epilogues keep reading y (register budget of the persistent kernels)
+  pl->cp.fuse_gamma = gamma;
+  pl->cp.fuse_beta = beta;
   return 0;
 }
 

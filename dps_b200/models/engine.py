@@ -299,7 +299,10 @@ class ResNetEngine:
 
         def fuse(plan, unit):          # unit: the conv+BN unit whose BN consumes this dgrad's output
             b = unit["bn"]
-            return plan.fuse_bn_bwd(unit["a"], unit["c"], b.mean, b.rstd, b.bsums)
+            plan.fuse_bn_bwd(unit["a"], unit["c"], b.mean, b.rstd, b.bsums)
+            if unit["residual"] is None and unit["relu"]:      # bn1 of a block / the stem: mask from x, y is not read
+                plan.mask_from_x(b.gamma, b.beta)
+            return plan
 
         self._side_plans = set()                 # weight-gradient plans: leaves of the backward graph
         nseg = len(self.segment_boundaries) - 1

@@ -29,6 +29,7 @@ def _decl() -> None:
     L.declare("dps_conv_plan_run", i32, [P, P])
     L.declare("dps_conv_plan_fuse_bn_bwd", i32, [P, P, P, P, P, P])
     L.declare("dps_conv_plan_addend_compact", i32, [P, i32])
+    L.declare("dps_conv_plan_fuse_bn_mask_from_x", i32, [P, P, P])
     L.declare("dps_conv_plan_destroy", i32, [P])
     L.declare("dps_conv_plan_info", i32, [P, C.POINTER(i32 * 3), C.POINTER(i32), C.POINTER(i32)])
     _declared = True
@@ -91,6 +92,13 @@ class ConvPlan:
         L.check(L.lib().dps_conv_plan_fuse_bn_bwd(C.c_void_p(self.handle), _ptr(y), _ptr(x), _ptr(mean), _ptr(rstd),
                                                   _ptr(sums)), "conv_plan_fuse_bn_bwd")
         self._keep = self._keep + (y, x, mean, rstd, sums)
+        return self
+
+    def mask_from_x(self, gamma, beta) -> "ConvPlan":
+        """after fuse_bn_bwd, for a BN without residual input: the ReLU mask is recomputed from x, y is not read."""
+        L.check(L.lib().dps_conv_plan_fuse_bn_mask_from_x(C.c_void_p(self.handle), _ptr(gamma), _ptr(beta)),
+                "conv_plan_fuse_bn_mask_from_x")
+        self._keep = self._keep + (gamma, beta)
         return self
 
     def addend_compact(self, on: bool = True) -> "ConvPlan":

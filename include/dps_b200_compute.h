@@ -28,6 +28,9 @@ int dps_wgrad_plan_create(const void* x, const void* dy, float* dw, int N, int H
  * accumulates [2C] int64 sums x 2^40) / take the addend at half resolution for parity (0,0) (stride-2 only). */
 int dps_conv_plan_fuse_bn_bwd(void* plan, const void* y, const void* x, const float* mean, const float* rstd,
                               long long* sums);
+/* after dps_conv_plan_fuse_bn_bwd, for a BN WITHOUT residual input: recompute the ReLU mask from x (needs that BN's
+ * gamma / beta, fp32 [C]) instead of reading its forward output y */
+int dps_conv_plan_fuse_bn_mask_from_x(void* plan, const float* gamma, const float* beta);
 int dps_conv_plan_addend_compact(void* plan, int on);
 int dps_conv_plan_run(void* plan, void* stream);
 int dps_conv_plan_destroy(void* plan);

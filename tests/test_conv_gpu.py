@@ -240,3 +240,42 @@ def test_all_passes_at_the_training_batch(shape):
     assert _relerr(out, y_ref) < 1.5e-2, ("fprop", _relerr(out, y_ref))
     assert _relerr(dx, dx_want) < 2e-2, ("dgrad", _relerr(dx, dx_want))
     assert _relerr(dw, dw_ref) < 5e-3, ("wgrad", _relerr(dw, dw_ref))
+
+
+@pytest.mark.parametrize("shape", [(16, 128, 128, 3, 1), (8, 256, 256, 3, 1), (4, 512, 512, 3, 1)],
+                         ids=lambda s: "H%d_%d->%d_k%d_s%d" % s)
+def test_fused_bn_backward_mask_recomputed_from_x(shape):
+    """A BatchNorm without residual input: the fused dgrad epilogue recomputes the ReLU mask from x
+    (y = relu(x*sc + sh) > 0) and never reads y.  Oracle: dz = dx * (bn(x) > 0) in fp32 torch, and the same sums."""
+    from dps_b200.ops.conv import ConvPlan
+    H, Cin, Cout, R, stride = shape
+    Nb = 32
+    g = torch.Generator(device="cuda").manual_seed(5)
+    w = (torch.randn(Cout, R, R, Cin, device="cuda", generator=g) / (R * R * Cin) ** 0.5).to(torch.bfloat16)
+    dy = torch.randn(Nb, H, H, Cout, device="cuda", generator=g).to(torch.bfloat16)
+    wf = w.float().permute(0, 3, 1, 2).contiguous()
+    dx_ref = torch.nn.grad.conv2d_input((Nb, Cin, H, H), wf, dy.float().permute(0, 3, 1, 2).contiguous(),
+                                        padding=1).permute(0, 2, 3, 1)
+    xbn = (torch.randn(Nb, H, H, Cin, device="cuda", generator=g) * 1.3 + 0.2).to(torch.bfloat16)
+    mean = xbn.float().reshape(-1, Cin).mean(0)
+    rstd = (xbn.float().reshape(-1, Cin).var(0, unbiased=False) + 1e-5).rsqrt()
+    gamma = torch.rand(Cin, device="cuda", generator=g) + 0.5
+    gamma[::7] *= -1.0                                       # negative scales flip the mask: must be honoured
+    beta = torch.randn(Cin, device="cuda", generator=g) * 0.3
+    sc = gamma * rstd
+    pre = xbn.float() * sc + (beta - mean * sc)
+    poison = torch.full_like(xbn, float("nan"))              # y must not be read on this path
+    sums = torch.zeros(2 * Cin, device="cuda", dtype=torch.int64)
+    dz = torch.empty(Nb, H, H, Cin, device="cuda", dtype=torch.bfloat16)
+    plan = ConvPlan.dgrad(dy, w, dz, N=Nb, H=H, W=H, Cin=Cin, Cout=Cout, R=R, stride=1)
+    plan.fuse_bn_bwd(poison, xbn, mean, rstd, sums).mask_from_x(gamma, beta).run()
+    torch.cuda.synchronize()
+    want = dx_ref * (pre > 0)
+    # elements whose pre-activation is within rounding of zero may fall on either side of the mask
+    sure = pre.abs() > 1e-3
+    assert _relerr(dz.float() * sure, want * sure) < 2e-2
+    dzf = dz.float().reshape(-1, Cin)
+    xhat = (xbn.float().reshape(-1, Cin) - mean) * rstd
+    got = sums.double() / 2 ** 40
+    assert torch.allclose(got[:Cin].float(), dzf.sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
+    assert torch.allclose(got[Cin:].float(), (dzf * xhat).sum(0), rtol=2e-3, atol=5e-2 * (Nb / 8) ** 0.5)
