@@ -10,6 +10,8 @@ gradient arena, both laid out by ``store/shardmap.py`` -- exactly what the Push/
 """
 from __future__ import annotations
 
+import os
+
 import ctypes as C
 from dataclasses import dataclass
 from typing import Callable, Dict, List, Optional, Tuple
@@ -300,7 +302,8 @@ class ResNetEngine:
         def fuse(plan, unit):          # unit: the conv+BN unit whose BN consumes this dgrad's output
             b = unit["bn"]
             plan.fuse_bn_bwd(unit["a"], unit["c"], b.mean, b.rstd, b.bsums)
-            if unit["residual"] is None and unit["relu"]:      # bn1 of a block / the stem: mask from x, y is not read
+            if unit["residual"] is None and unit["relu"] and os.environ.get("DPS_MASK_X", "1") != "0":
+                # bn1 of a block / the stem: the mask is recomputed from x, y is not read
                 plan.mask_from_x(b.gamma, b.beta)
             return plan
 
