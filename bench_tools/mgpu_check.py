@@ -13,7 +13,8 @@ from dps_b200.api import Job
 
 mode, out_path = sys.argv[1], sys.argv[2]
 B, steps = 16, (int(sys.argv[3]) if len(sys.argv) > 3 else 3)
-cfg = Config(mode=mode, batch_size=B, lr=0.05, barrier_timeout_s=20.0, use_cuda_graph=True)
+cfg = Config(mode=mode, batch_size=B, lr=0.05, barrier_timeout_s=20.0, use_cuda_graph=True,
+             nvls=os.environ.get("DPS_NVLS", "off"))        # 'auto' / 'on': pull broadcast through the NVLS window
 job = Job(cfg)
 rank, world, dev = job.rank, job.world, job.device
 g = torch.Generator().manual_seed(100 + rank)
@@ -65,7 +66,10 @@ if mode == "async":
     mine = job.ps.wbf16[rank].clone()
 ref0 = mine.clone()
 dist.broadcast(ref0, 0)
-same = torch.tensor([int(torch.equal(ref0, mine) and torch.equal(mine, master.to(torch.bfloat16)))], device=dev)
+ns = job.ps.n_small                                        # the fp32 prefix (BN affine, fc bias) travels with the weights
+small_ok = mode != "sync" or torch.equal(job.ps.small[rank][:ns], master[:ns])
+same = torch.tensor([int(torch.equal(ref0, mine) and torch.equal(mine, master.to(torch.bfloat16)) and small_ok)],
+                    device=dev)
 dist.all_reduce(same, op=dist.ReduceOp.MIN)
 st = job.ps.async_stats() if mode == "async" else {"async_updates": 0, "rejected_updates": 0}
 hist = st.get("staleness_histogram", {})
@@ -82,7 +86,7 @@ if rank == 0:
            "rejected": [int(t[3]) for t in allinfo], "dropped": [int(t[4]) for t in allinfo],
            "torn_pulls": [int(t[5]) for t in allinfo], "hist_total": [int(t[6]) for t in allinfo],
            "max_staleness": [int(t[7]) for t in allinfo], "versions_monotone": [int(t[8]) for t in allinfo],
-           "world": world, "staleness_bound": cfg.staleness_bound, **extra}
+           "world": world, "staleness_bound": cfg.staleness_bound, "nvls_pull": bool(job.ps.nvls), **extra}
     with open(out_path, "w") as f:
         json.dump(res, f)
     print(json.dumps(res))

@@ -340,6 +340,13 @@ __device__ __forceinline__ void st_v4(void* p, uint4 v) {
   asm volatile("st.global.v4.u32 [%0], {%1,%2,%3,%4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w)
                : "memory");
 }
+// One store that the NVSwitch replicates into every GPU bound to the multicast object behind `p` (NVLS).  `p` is an
+// address inside the multicast mapping, not a peer pointer.  Weak ordering: publish with a system-scope fence + signal.
+__device__ __forceinline__ void multimem_st_v4(void* p, uint4 v) {
+  asm volatile("multimem.st.weak.global.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(p), "r"(v.x), "r"(v.y), "r"(v.z),
+               "r"(v.w)
+               : "memory");
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -255,6 +255,18 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
   }
 }
 
+// NVLS form of the broadcast: ONE multimem.st per vector through the multicast window; the switch replicates it into
+// every worker's arena (this GPU's included), so the owner's egress is E*2 bytes instead of (W-1)*E*2.
+__device__ __forceinline__ void bcast_mc(const DpsTables& T, long long g, long long n_small, uint4 h, const F8& p) {
+  multimem_st_v4(T.mc_wbf16 + g, h);
+  if (g < n_small) {
+    multimem_st_v4(T.mc_small + g, make_uint4(__float_as_uint(p.v[0]), __float_as_uint(p.v[1]), __float_as_uint(p.v[2]),
+                                              __float_as_uint(p.v[3])));
+    multimem_st_v4(T.mc_small + g + 4, make_uint4(__float_as_uint(p.v[4]), __float_as_uint(p.v[5]),
+                                                  __float_as_uint(p.v[6]), __float_as_uint(p.v[7])));
+  }
+}
+
 // ------------------------------------------------------------------------------------------
 // PULL: owner casts its fp32 shard to bf16 and stores it into every worker's weight arena
 // (plus an fp32 copy of the "small" head of the arena: BN affine parameters and fc bias).
@@ -273,6 +285,10 @@ __global__ void __launch_bounds__(256) pull_bcast_kernel(const __grid_constant__
       const long long g = global_index(l, o, W, BS);
       const F8 p = load_f32x8(master + l);
       const uint4 h = to_bf16x8(p);
+      if (T.mc_wbf16) {
+        bcast_mc(T, g, n_small, h, p);
+        continue;
+      }
       for (int ww = 0; ww < W; ++ww) {
         const int w = (o + ww) % W;                          // start with the local copy, then peers
         st_v4(T.wbf16[w] + g, h);
@@ -318,6 +334,10 @@ __global__ void __launch_bounds__(256) pull_seg_kernel(const __grid_constant__ D
           if (l >= hi) break;
           const long long g = global_index(l, o, W, BS);
           const uint4 h = to_bf16x8(p[j]);
+          if (T.mc_wbf16) {
+            bcast_mc(T, g, n_small, h, p[j]);
+            continue;
+          }
           for (int ww = 0; ww < W; ++ww) {
             const int w = (o + ww) % W;
             st_v4(T.wbf16[w] + g, h);
@@ -638,6 +658,7 @@ __global__ void __launch_bounds__(256) publish_kernel(const __grid_constant__ Dp
 using namespace dps;
 
 DPS_API const char* dps_last_error(void) { return g_dps_err; }
+DPS_API int dps_tables_size(void) { return (int)sizeof(DpsTables); }   // checked against the ctypes mirror at load
 
 static int check_tables(const DpsTables* T) {
   if (!T) DPS_FAIL(1, "null tables");

@@ -75,6 +75,7 @@ class Config:
     async_server: bool = True             # async mode: the owner role runs on its own high-priority stream (apply on arrival)
     async_server_period_us: int = 100     # pause between two scans of the arrival ring by the server thread
     staleness_policy: str = "reference"   # 'reference' | 'world' (bound + W-1) | 'batch' (one version per drained batch)
+    nvls: str = "off"                     # pull broadcast through an NVLS multicast window: 'off' | 'auto' | 'on'
     serve_port: Optional[int] = None      # device path: rank 0 also serves the gRPC contract on this port (0 = any free)
     remote_slots: int = 0                 # source slots for remote workers attached through that door (sync mode)
     # ---- outputs -----------------------------------------------------------
@@ -103,6 +104,8 @@ class Config:
             raise ValueError("amp must be none|bf16")
         if self.staleness_policy not in ("reference", "world", "batch"):
             raise ValueError("staleness_policy must be reference|world|batch")
+        if self.nvls not in ("off", "auto", "on"):
+            raise ValueError("nvls must be off|auto|on")
         if self.sync_steps < 1:
             raise ValueError("sync_steps must be >= 1")
         return self
@@ -171,6 +174,9 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
                    help="async mode: reference = reject staleness > bound; world = bound widened by W-1 (W workers put "
                         "W-1 updates between a pull and the next push by construction); batch = arrivals drained "
                         "together count as one version")
+    p.add_argument("--nvls", choices=["off", "auto", "on"], default="off",
+                   help="on-box job: pull broadcast through an NVLS multicast window (one multimem.st per vector "
+                        "instead of W peer stores); auto = when the box supports it")
     p.add_argument("--serve-port", type=int, default=None,
                    help="on-box job: rank 0 also serves the gRPC contract on this port (remote / CPU workers)")
     p.add_argument("--remote-slots", type=int, default=0,

@@ -43,6 +43,7 @@ class DpsTables(C.Structure):
         ("ring", _PtrArray), ("wbf16", _PtrArray), ("small", _PtrArray), ("pub", _PtrArray),
         ("pubsmall", _PtrArray), ("flags", _PtrArray),
         ("step_ctr", _P), ("lr_ptr", _P),
+        ("mc_wbf16", _P), ("mc_small", _P),
     ]
 
 
@@ -59,6 +60,7 @@ def _declare(lib: C.CDLL) -> None:
     TP = C.POINTER(DpsTables)
     sigs = {
         "dps_last_error": (C.c_char_p, []),
+        "dps_tables_size": (i32, []),
         "dps_device_count": (i32, [C.POINTER(i32)]),
         "dps_arena_alloc": (i32, [i32, u64, C.POINTER(_P)]),
         "dps_arena_free": (i32, [i32, _P]),
@@ -96,6 +98,9 @@ def lib() -> C.CDLL:
                         "(device ops have no fallback)")
                 l = C.CDLL(LIB_PATH)
                 _declare(l)
+                if l.dps_tables_size() != C.sizeof(DpsTables):
+                    raise NativeError(f"DpsTables: library has {l.dps_tables_size()} bytes, the ctypes mirror "
+                                      f"{C.sizeof(DpsTables)}; rebuild with `python -m dps_b200.build`")
                 _lib = l
     return _lib
 

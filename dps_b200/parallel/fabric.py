@@ -120,3 +120,66 @@ class Fabric:
         for p in self._owned:
             self.lib.dps_arena_free(self.device_index, C.c_void_p(p))
         self._opened, self._owned = [], []
+
+
+class MulticastArena:
+    """The pull destinations (bf16 weight arena + fp32 small prefix) in memory that is ALSO bound to an NVLS
+    multicast object, so an owner stores each vector once (``multimem.st``, csrc/ps_kernels.cu: bcast_mc) and the
+    NVSwitch replicates it into every worker's replica -- the in-switch form of the reference's "send the whole model
+    to every worker" (reference: src/parameter_server/server.py:221-230 -> src/workers/worker.py:233-262).
+
+    Allocation, handle exchange and the multicast binding (cuMemCreate / cuMulticastCreate / cuMulticastBindMem) are
+    done by ``torch.distributed._symmetric_memory`` -- bootstrap plumbing, like the IPC handle exchange of ``Fabric``;
+    the kernels only see three kinds of address: this rank's replica, the peers' replicas (unicast mappings, still used
+    by the per-peer path and the async gather), and the multicast window ``mc_base``.
+
+    ``mc_base == 0`` when the box has no multicast support (no NVSwitch / fabric manager without NVLS): the arena then
+    works as plain peer memory and the kernels keep their per-peer stores.
+    """
+
+    def __init__(self, rank: int, world: int, device_index: int, spec: ArenaSpec, group=None):
+        import torch.distributed as dist
+        import torch.distributed._symmetric_memory as symm
+        self.rank, self.world, self.device_index, self.spec = rank, world, device_index, spec
+        self.device = torch.device("cuda", device_index)
+        torch.cuda.set_device(self.device)
+        size = (spec.size + 4095) // 4096 * 4096
+        # one whole allocation of our own (not a slice of torch's symmetric-memory pool): base address == tensor address
+        from torch._C._distributed_c10d import _SymmetricMemory
+        self.buf = _SymmetricMemory.empty_strided_p2p((size,), (1,), torch.uint8, self.device)
+        self.buf.zero_()
+        torch.cuda.synchronize(self.device)
+        self.handle = symm.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+        self.bases: List[int] = [int(p) for p in self.handle.buffer_ptrs]
+        if self.bases[rank] != self.buf.data_ptr():
+            raise RuntimeError("symmetric memory: the local mapping is not the tensor that was allocated")
+        mc = int(self.handle.multicast_ptr or 0)
+        # every rank must take the same path: multicast only if all of them got a window
+        ok = torch.tensor([1 if mc else 0], dtype=torch.int32, device=self.device)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN, group=group)
+        self.mc_base = mc if int(ok.item()) else 0
+
+    @staticmethod
+    def supported(device_index: int) -> bool:
+        try:
+            from torch._C._autograd import DeviceType
+            from torch._C._distributed_c10d import _SymmetricMemory
+            return bool(_SymmetricMemory.has_multicast_support(DeviceType.CUDA, device_index))
+        except Exception:
+            return False
+
+    def ptr(self, rank: int, region: str) -> int:
+        return self.bases[rank] + self.spec.regions[region].offset
+
+    def mc_ptr(self, region: str) -> int:
+        return self.mc_base + self.spec.regions[region].offset if self.mc_base else 0
+
+    def tensor(self, rank: int, region: str, dtype: torch.dtype) -> torch.Tensor:
+        reg = self.spec.regions[region]
+        itemsize = torch.empty((), dtype=dtype).element_size()
+        return tensor_from_ptr(self.ptr(rank, region), reg.nbytes // itemsize, dtype, self.device)
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        self.handle = None
+        self.buf = None

@@ -23,7 +23,7 @@ import torch
 from ..config import Config
 from ..ops import _lib as L
 from ..store.shardmap import Layout
-from .fabric import ArenaSpec, Fabric
+from .fabric import ArenaSpec, Fabric, MulticastArena
 
 
 def _default_ctas(shard_elems: int) -> int:
@@ -62,14 +62,38 @@ class DevicePS:
         spec.add("stage", (world + self.n_extra) * self.E * (2 if self.compress else 4))
         if self.n_extra:
             spec.add("master", self.E * 4)
-        spec.add("wbf16", self.total * 2)
-        spec.add("small", max(self.n_small, 8) * 4)
+        # NVLS (Config.nvls): the two pull destinations live in a multicast-bound arena instead, so the owner's
+        # broadcast is one multimem.st per vector.  'auto' = use it when the box supports multicast, 'on' = require it.
+        want_mc = cfg.nvls != "off" and world > 1 and not emulate
+        self.mc: Optional[MulticastArena] = None
+        if want_mc:
+            try:
+                if not MulticastArena.supported(device_index):
+                    raise RuntimeError("this device reports no multicast support")
+                mspec = ArenaSpec()
+                mspec.add("wbf16", self.total * 2)
+                mspec.add("small", max(self.n_small, 8) * 4)
+                self.mc = MulticastArena(rank, world, device_index, mspec, group=group)
+                if not self.mc.mc_base:
+                    raise RuntimeError("no multicast window could be mapped")
+            except Exception as e:
+                if cfg.nvls == "on":
+                    raise RuntimeError(f"Config.nvls='on': {e}") from e
+                import sys
+                print(f"[dps_b200] rank {rank}: NVLS pull not available ({e!r}); per-peer stores", file=sys.stderr, flush=True)
+                self.mc = None
+            want_mc = self.mc is not None
+        if not want_mc:
+            spec.add("wbf16", self.total * 2)
+            spec.add("small", max(self.n_small, 8) * 4)
         if self.is_async:
             spec.add("ring", self.R * self.E * 2)
             spec.add("pub", self.E * 2)
             spec.add("pubsmall", max(self.n_small, 8) * 4)
         self.fabric = Fabric(rank, world, device_index, spec, emulate=emulate, group=group)
         self.lib = self.fabric.lib
+        self.nvls = bool(self.mc is not None and self.mc.mc_base)
+        warena = self.mc if self.mc is not None else self.fabric      # where wbf16 / small live
 
         # local-only buffers
         self.local = list(self.fabric.local_ranks())
@@ -82,8 +106,8 @@ class DevicePS:
             self.master = {r: torch.zeros(self.E, dtype=torch.float32, device=dev) for r in self.local}
         self.mom: Dict[int, torch.Tensor] = {r: torch.zeros(self.E, dtype=torch.float32, device=dev)
                                              for r in self.local}
-        self.wbf16 = {r: self.fabric.tensor(r, "wbf16", torch.bfloat16) for r in self.local}
-        self.small = {r: self.fabric.tensor(r, "small", torch.float32) for r in self.local}
+        self.wbf16 = {r: warena.tensor(r, "wbf16", torch.bfloat16) for r in self.local}
+        self.small = {r: warena.tensor(r, "small", torch.float32) for r in self.local}
         self.flags = {r: self.fabric.tensor(r, "flags", torch.int32) for r in self.local}
         for r in self.local:                 # membership: every source is waited for until it misses a barrier
             self.flags[r][L.F_ALIVE] = (1 << world) - 1 if world < 32 else -1
@@ -94,8 +118,8 @@ class DevicePS:
         t.rank_lo, t.rank_hi = (0, world) if emulate else (rank, rank + 1)
         for r in range(world):
             t.stage[r] = self.fabric.ptr(r, "stage")
-            t.wbf16[r] = self.fabric.ptr(r, "wbf16")
-            t.small[r] = self.fabric.ptr(r, "small")
+            t.wbf16[r] = warena.ptr(r, "wbf16")
+            t.small[r] = warena.ptr(r, "small")
             t.flags[r] = self.fabric.ptr(r, "flags")
             if self.is_async:
                 t.ring[r] = self.fabric.ptr(r, "ring")
@@ -105,6 +129,8 @@ class DevicePS:
             t.grad[r] = self.grad[r].data_ptr()
             t.master[r] = self.master[r].data_ptr()
             t.mom[r] = self.mom[r].data_ptr()
+        if self.nvls:
+            t.mc_wbf16, t.mc_small = self.mc.mc_ptr("wbf16"), self.mc.mc_ptr("small")
         # device-resident round counters + learning rate (graph replay needs no baked-in step / lr)
         self.step_ctr = torch.zeros(4, dtype=torch.int32, device=dev)
         self.lr_dev = torch.full((1,), float(cfg.lr), dtype=torch.float32, device=dev)
@@ -413,4 +439,6 @@ class DevicePS:
 
     def close(self) -> None:
         self.stop_async_server()
+        if self.mc is not None:
+            self.mc.close()
         self.fabric.close()

@@ -89,9 +89,15 @@ typedef struct DpsTables {
    * dps_wait_pull with bump=1), step_ctr[1] = this rank's async push count (bumped by dps_async_apply). */
   uint32_t* step_ctr;
   const float* lr_ptr;
+  /* Optional NVLS window: the multicast address of the bf16 weight arena / fp32 small prefix.  One multimem.st through
+   * it lands in EVERY worker's wbf16 / small (same offsets), so the pull stores each vector once instead of W times.
+   * NULL = per-peer stores. */
+  uint16_t* mc_wbf16;
+  float* mc_small;
 } DpsTables;
 
 const char* dps_last_error(void);
+int dps_tables_size(void);                 /* sizeof(DpsTables): bindings check their mirror of the struct against it */
 
 /* ---- fabric (reference: the gRPC channel/server runtime, server.py:370-403, worker.py:199-231) ---- */
 int dps_device_count(int* n);
