@@ -16,10 +16,11 @@ def _ngpu():
     return torch.cuda.device_count() if torch.cuda.is_available() else 0
 
 
-def _torchrun(n, script_args, port=29631, timeout=600):
+def _torchrun(n, script_args, port=29631, timeout=600, env=None):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={n}",
            "--master-addr", "127.0.0.1", "--master-port", str(port)] + script_args
-    return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout)
+    return subprocess.run(cmd, cwd=ROOT, capture_output=True, text=True, timeout=timeout,
+                          env=dict(os.environ, **(env or {})))
 
 
 @pytest.mark.parametrize("world", [2, 4, 8])
@@ -48,6 +49,29 @@ def test_multi_rank_job_over_ipc(mode, world, tmp_path):
         assert res["hist_total"] == [a + b for a, b in zip(res["accepted"], res["rejected"])]
         assert res["versions"] == res["accepted"] and all(v > 0 for v in res["versions"])
         assert res["versions_monotone"] == [1] * world and res["torn_pulls"] == [0] * world
+
+
+@pytest.mark.parametrize("mode", ["sync", "async"])
+def test_pull_through_the_nvls_multicast_window(mode, tmp_path):
+    """Config.nvls: the weight arena + fp32 prefix live in a multicast-bound arena and the owners broadcast with one
+    multimem.st per vector.  Same invariants as the per-peer path: every replica (bf16 arena AND fp32 prefix) equals
+    the sharded master after the last pull, the first sync step equals the mean-gradient step.  Skips when the box
+    has no multicast support (the job then falls back to per-peer stores and says so)."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = tmp_path / f"res_nvls_{mode}.json"
+    r = _torchrun(2, [os.path.join(ROOT, "bench_tools", "mgpu_check.py"), mode, str(out), "20"],
+                  port=29671 + (mode == "async"), env={"DPS_NVLS": "auto"})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads(out.read_text())
+    if not res["nvls_pull"]:
+        pytest.skip("no NVLS multicast on this box: " + r.stderr[-300:])
+    assert res["error_bits"] == [0, 0] and res["replicas_equal"] and res["finite"]
+    if mode == "sync":
+        assert res["versions"] == [20, 20]
+        assert res["max_abs_diff_vs_single_process_mean_step"] < 2e-3
+    else:
+        assert res["torn_pulls"] == [0, 0] and res["versions_monotone"] == [1, 1]
 
 
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
