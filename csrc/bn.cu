@@ -378,9 +378,11 @@ DPS_API int dps_bn_backward_noalloc(const void* dy, const void* y, const void* x
   // the shared array still holds the previous call's sums: clear exactly what this call accumulates into
   DPS_CHECK(cudaMemsetAsync(sums, 0, sizeof(long long) * 2 * (size_t)C, st));
   const int g1 = bn_reduce_grid(P, C);
-  DPS_CHECK(launch_pdl(bn_bwd_reduce_kernel, dim3(g1), dim3(kBnThreads), 0, st, (const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
-                                                  (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz, sums, P, C,
-                                                  relu));
+  // plain launch: it follows a memset, not a kernel, so there is no programmatic edge to give it (and a captured graph
+  // gets an ordinary memset -> kernel dependency); the apply kernel behind it still overlaps its launch with this one
+  bn_bwd_reduce_kernel<<<dim3(g1), dim3(kBnThreads), 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)y,
+                                                             (const __nv_bfloat16*)x, mean, rstd, (__nv_bfloat16*)dz, sums,
+                                                             P, C, relu);
   DPS_CHECK(cudaGetLastError());
   DPS_CHECK(launch_pdl(bn_bwd_apply_kernel, dim3(bn_grid(P * (C / 8))), dim3(kBnThreads), 0, st, (const __nv_bfloat16*)(relu ? dz : dy),
                                                                   (const __nv_bfloat16*)x, mean, rstd, gamma, sums,

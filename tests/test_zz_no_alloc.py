@@ -88,6 +88,41 @@ def test_noalloc_bn_backward_matches_existing_entry_point_twice_in_a_row():
             assert float((a.float() - b).abs().max()) <= tol, (name, Cc, float((a.float() - b).abs().max()), tol)
 
 
+def test_noalloc_two_consecutive_calls_replayed_from_a_captured_graph():
+    """The memset + two kernels of each call become graph nodes; two calls back to back share the built-in array, so
+    the second call's memset must be ordered behind the first call's apply kernel in the captured graph as well.
+    Replayed three times: every replay must reproduce the eager results of both calls."""
+    lib, L = _lib()
+    cases = [(4096, 128, 11), (1024, 512, 12)]
+    data = [_case(P, Cc, seed) for P, Cc, seed in cases]
+    eager = [_run(lib, L, True, *d, P, Cc) for d, (P, Cc, _) in zip(data, cases)]     # also resolves the symbol address
+    outs = []
+    for d, (P, Cc, _) in zip(data, cases):
+        dy = d[2]
+        outs.append((torch.empty_like(dy), torch.empty_like(dy), torch.zeros(Cc, device="cuda"),
+                     torch.zeros(Cc, device="cuda")))
+    p = lambda t: C.c_void_p(t.data_ptr())
+    side = torch.cuda.Stream()
+    side.wait_stream(torch.cuda.current_stream())
+    graph = torch.cuda.CUDAGraph()
+    with torch.cuda.stream(side):
+        with torch.cuda.graph(graph, stream=side):
+            st = C.c_void_p(L.stream_ptr())
+            for (x, y, dy, mean, rstd, gamma), (dz, dx, dgamma, dbeta), (P, Cc, _) in zip(data, outs, cases):
+                rc = lib.dps_bn_backward_noalloc(p(dy), p(y), p(x), p(mean), p(rstd), p(gamma), p(dz), p(dx),
+                                                 p(dgamma), p(dbeta), P, Cc, 1, st)
+                assert rc == 0, lib.dps_last_error()
+    for _ in range(3):
+        for dz, dx, dgamma, dbeta in outs:
+            dz.fill_(float("nan")), dx.fill_(float("nan"))
+            dgamma.zero_(), dbeta.zero_()                 # the entry point ACCUMULATES into dgamma / dbeta
+        graph.replay()
+        torch.cuda.synchronize()
+        for got, want, (P, Cc, _) in zip(outs, eager, cases):
+            for name, a, b in zip(("dz", "dx", "dgamma", "dbeta"), got, want):
+                assert torch.equal(a, b), (name, Cc)      # integer fixed-point sums: bit-identical to the eager calls
+
+
 def test_noalloc_rejects_channel_counts_beyond_the_built_in_scratch():
     lib, L = _lib()
     t = torch.zeros(8, device="cuda")
