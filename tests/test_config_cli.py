@@ -61,3 +61,25 @@ def test_job_without_cuda_points_to_the_grpc_path():
         pytest.skip("CUDA present")
     with pytest.raises(RuntimeError, match="gRPC roles"):
         Job(Config(workers=1), rank=0, world=1, device_index=0)
+
+
+def test_nvls_flag_parses_and_validates():
+    import argparse
+    p = argparse.ArgumentParser()
+    CFG.add_server_args(p)
+    CFG.add_common_args(p)
+    assert CFG.from_args(p.parse_args([])).nvls == "off"            # per-peer stores measured faster: off by default
+    assert CFG.from_args(p.parse_args(["--nvls", "auto"])).nvls == "auto"
+    with pytest.raises(ValueError):
+        CFG.Config(nvls="maybe").validate()
+
+
+def test_ctypes_mirror_of_the_pointer_tables_matches_the_library():
+    """The kernels take DpsTables by value: a field added on one side only would shift every pointer after it."""
+    import ctypes
+    from dps_b200.ops import _lib as L
+    if not L.available():
+        pytest.skip("native library not built")
+    assert L.lib().dps_tables_size() == ctypes.sizeof(L.DpsTables)
+    names = [f[0] for f in L.DpsTables._fields_]
+    assert names[-2:] == ["mc_wbf16", "mc_small"] and names.index("flags") < names.index("step_ctr")
