@@ -73,15 +73,21 @@ def main():
             f.write(f"| {i} | `{name}` | {d[idx['Grid Size']]} x {d[idx['Block Size']]} | {regs:.0f} | {smem:.0f} | {t * 1e6:.2f} | "
                     f"{tp_a:.1f}% ({tp_e:.1f}%) | {smb:.1f}% | {l2:.1f}% | {dr:.1f}% | {gbs:.0f} ({gbs / PEAKS['hbm_gbs']:.2f}) | "
                     f"{wa:.1f}% | {st} |\n")
-            a = agg.setdefault(name, [0, 0.0, 0.0, 0.0])
+            a = agg.setdefault(name, [0, 0.0, 0.0, 0.0, 0.0])
             a[0] += 1
             a[1] += t * 1e6
             a[2] += tp_a
             a[3] += gbs
-        f.write("\n## per kernel\n\n| kernel | launches | mean us | mean tensor pipe active | = bf16 TFLOP/s at the sustained cuBLAS rate | mean DRAM GB/s |\n"
-                "|---|---:|---:|---:|---:|---:|\n")
-        for name, (n, t, tp, gb) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
-            f.write(f"| `{name}` | {n} | {t / n:.2f} | {tp / n:.1f}% | {tp / n / 100 * PEAKS['bf16_tflops_sustained']:.0f} | {gb / n:.0f} |\n")
+            a[4] += tp_e
+        nominal = 2250.0       # dense bf16 TFLOP/s of the tensor pipe at 100 % activity on every SM
+        f.write("\n## per kernel\n\nAchieved rate = tensor-pipe activity over the ELAPSED cycles of all 148 SMs x the nominal dense bf16 peak "
+                f"({nominal:.0f} TFLOP/s); cuBLAS itself sustains {PEAKS['bf16_tflops_sustained']:.0f} on a large GEMM.\n\n"
+                "| kernel | launches | mean us | tensor pipe active (while the SM is busy) | over elapsed | achieved TFLOP/s | of the sustained "
+                "cuBLAS rate | mean DRAM GB/s |\n|---|---:|---:|---:|---:|---:|---:|---:|\n")
+        for name, (n, t, tp, gb, te) in sorted(agg.items(), key=lambda kv: -kv[1][1]):
+            ach = te / n / 100 * nominal
+            f.write(f"| `{name}` | {n} | {t / n:.2f} | {tp / n:.1f}% | {te / n:.1f}% | {ach:.0f} | "
+                    f"{ach / PEAKS['bf16_tflops_sustained']:.2f} | {gb / n:.0f} |\n")
     print(open(out).read()[:2500])
 
 
