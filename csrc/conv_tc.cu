@@ -777,7 +777,7 @@ __global__ void __launch_bounds__(64 + 32 * EPI) pairconv_kernel(const __grid_co
 // padding).  Each filter tap is then just a *shifted window* of that halo tile: the UMMA A descriptor starts at
 // ((1+dh)*10 + (1+dw)) * 128 B with a stride-byte-offset of 10 * 128 B between 8-row groups -- one image row of the
 // 16x8 tile is one 8-row group.  (The 128-byte swizzle is a function of absolute shared-memory address bits, so
-// windows that are not 1024-byte aligned read correctly with base_offset = 0; probed in csrc/exp_halo.cu.)
+// windows that are not 1024-byte aligned read correctly with base_offset = 0; probed in bench_tools/exp/exp_halo.cu.)
 // Two 64-column TMEM accumulators and TWO epilogue groups of 8 warps (own staging tile, own named barrier): group g
 // drains accumulator g, so the epilogues of tiles i and i+1 are in flight together and overlap the MMAs of tile i+2.
 // The per-tile epilogue is a chain of latencies (TMEM load, staging round trip, three block barriers, global
