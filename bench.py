@@ -47,6 +47,7 @@ def parse_args(argv=None):
     p.add_argument("--staleness-policy", choices=["reference", "world", "batch"], default="reference")
     p.add_argument("--nvls", choices=["off", "auto", "on"], default="off",
                    help="pull broadcast through an NVLS multicast window (N > 1)")
+    p.add_argument("--nvls-reduce", action="store_true", help="with --nvls: push summed in the switch (multimem.ld_reduce)")
     p.add_argument("--no-e2e", action="store_true")
     p.add_argument("--no-graph", action="store_true", help="eager launches (for ncu launch lists)")
     return p.parse_args(argv)
@@ -109,7 +110,7 @@ def run_ours(args) -> dict:
     assert world == args.gpus, f"--gpus {args.gpus} but WORLD_SIZE={world}"
     cfg = Config(mode=args.mode, workers=world, batch_size=args.batch, lr=0.1, momentum=args.momentum,
                  image_size=args.image_size, barrier_timeout_s=30.0, staleness_policy=args.staleness_policy,
-                 nvls=args.nvls, use_cuda_graph=not args.no_graph)
+                 nvls=args.nvls, nvls_reduce=args.nvls_reduce, use_cuda_graph=not args.no_graph)
     factory = None
     if args.engine == "torch":
         from bench_tools.torch_engine import TorchEngine as factory
@@ -213,6 +214,7 @@ def run_ours(args) -> dict:
                    "mode": cfg.mode, "engine": args.engine, "optimizer": "SGD lr=0.1 momentum=%g" % args.momentum,
                    "compression": "fp16 push", "cuda_graph": bool(native_graph),
                    "nvls_pull": bool(getattr(job.ps, "nvls", False)),
+                   "nvls_reduce": bool(getattr(job.ps, "nvls_reduce", False)),
                    "l2": "no explicit flush: per-step working set %.0f MB of activations+gradients > 126 MB L2"
                          % (2 * wk.engine.activation_bytes() / 1e6 if hasattr(wk.engine, "activation_bytes") else 0),
                    "baseline_number": "%.1f img/s = reference %s run published in BASELINE.md" % (

@@ -14,7 +14,8 @@ from dps_b200.api import Job
 mode, out_path = sys.argv[1], sys.argv[2]
 B, steps = 16, (int(sys.argv[3]) if len(sys.argv) > 3 else 3)
 cfg = Config(mode=mode, batch_size=B, lr=0.05, barrier_timeout_s=20.0, use_cuda_graph=True,
-             nvls=os.environ.get("DPS_NVLS", "off"))        # 'auto' / 'on': pull broadcast through the NVLS window
+             nvls=os.environ.get("DPS_NVLS", "off"),        # 'auto' / 'on': pull broadcast through the NVLS window
+             nvls_reduce=os.environ.get("DPS_NVLS_REDUCE", "0") == "1")     # push summed in the switch
 job = Job(cfg)
 rank, world, dev = job.rank, job.world, job.device
 g = torch.Generator().manual_seed(100 + rank)
@@ -86,7 +87,8 @@ if rank == 0:
            "rejected": [int(t[3]) for t in allinfo], "dropped": [int(t[4]) for t in allinfo],
            "torn_pulls": [int(t[5]) for t in allinfo], "hist_total": [int(t[6]) for t in allinfo],
            "max_staleness": [int(t[7]) for t in allinfo], "versions_monotone": [int(t[8]) for t in allinfo],
-           "world": world, "staleness_bound": cfg.staleness_bound, "nvls_pull": bool(job.ps.nvls), **extra}
+           "world": world, "staleness_bound": cfg.staleness_bound, "nvls_pull": bool(job.ps.nvls),
+           "nvls_reduce": bool(job.ps.nvls_reduce), **extra}
     with open(out_path, "w") as f:
         json.dump(res, f)
     print(json.dumps(res))

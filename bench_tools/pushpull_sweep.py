@@ -27,6 +27,7 @@ p.add_argument("--out", default=None)
 p.add_argument("--iters", type=int, default=20)
 p.add_argument("--no-nccl", action="store_true")
 p.add_argument("--nvls", choices=["off", "auto", "on"], default="off", help="pull through the NVLS multicast window")
+p.add_argument("--nvls-reduce", action="store_true", help="push summed in the switch (multimem.ld_reduce)")
 p.add_argument("--kb", default="1,4,16,64,256,1024,4096,16384,65536", help="payload sizes in KB")
 a = p.parse_args()
 rank, world = int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
@@ -63,7 +64,7 @@ for kb in [int(v) for v in a.kb.split(",")]:
     BS = 512 if elems < world * 2048 else 2048
     total = max(world * BS, (elems + world * BS - 1) // (world * BS) * (world * BS))
     layout = Layout(entries={}, order=[], n_small=0, total=total, world=world, block_elems=BS)
-    cfg = Config(mode="sync", workers=world, lr=0.01, barrier_timeout_s=20.0, nvls=a.nvls)
+    cfg = Config(mode="sync", workers=world, lr=0.01, barrier_timeout_s=20.0, nvls=a.nvls, nvls_reduce=a.nvls_reduce)
     ps = DevicePS(layout, cfg, rank, world, local)
     ps.grad[rank].normal_()
 
@@ -89,7 +90,7 @@ for kb in [int(v) for v in a.kb.split(",")]:
     t_push, t_pull = float(t2[0]), float(t2[1])
     row = {"payload_bytes": total * 2, "world": world, "push_us": round(t_push, 2), "pull_us": round(t_pull, 2),
            "round_us": round(t_round, 2), "push_GBps": round(total * 2 / t_push / 1e3, 2),
-           "pull_GBps": round(total * 2 / t_pull / 1e3, 2), "error_bits": ps.error_bits(), "nvls_pull": bool(ps.nvls)}
+           "pull_GBps": round(total * 2 / t_pull / 1e3, 2), "error_bits": ps.error_bits(), "nvls_pull": bool(ps.nvls), "nvls_reduce": bool(ps.nvls_reduce)}
     wire = (world - 1) / world * total * 2
     for k, bw in LINK.items():
         tmin = wire / bw * 1e6
@@ -109,6 +110,6 @@ for kb in [int(v) for v in a.kb.split(",")]:
 if rank == 0 and a.out:
     os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)
     with open(a.out, "w") as f:
-        json.dump({"world": world, "nvls": a.nvls, "rows": rows}, f, indent=1)
+        json.dump({"world": world, "nvls": a.nvls, "nvls_reduce": a.nvls_reduce, "rows": rows}, f, indent=1)
 if world > 1:
     dist.destroy_process_group()

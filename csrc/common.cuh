@@ -347,6 +347,16 @@ __device__ __forceinline__ void multimem_st_v4(void* p, uint4 v) {
                "r"(v.w)
                : "memory");
 }
+// One load that the NVSwitch answers with the SUM over every GPU bound to the multicast object behind `p` (NVLS
+// in-switch reduction): eight fp16 values per call, accumulated in fp32 inside the switch, returned as 4 x f16x2.
+__device__ __forceinline__ uint4 multimem_ld_reduce_f16x8(const void* p) {
+  uint4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.acc::f32.v4.f16x2 {%0, %1, %2, %3}, [%4];"
+               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
+               : "l"(p)
+               : "memory");
+  return v;
+}
 __device__ __forceinline__ uint32_t ld_acquire_sys(const uint32_t* p) {
   uint32_t v;
   asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");

@@ -138,7 +138,9 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     float* grad = T.grad[r];
     for (int oo = 0; oo < W; ++oo) {
       const int o = (r + 1 + oo) % W;                        // rotate so owners are hit evenly
-      uint16_t* dst = T.stage[o] + (long long)r * E;           // peer-mapped staging slot [src=r]
+      // peer-mapped staging slot [src=r] on the owner -- or, with the NVLS reduction, slot [owner=o] of this rank's OWN
+      // replica of the multicast-bound staging arena (local stores only; the owner sums the replicas in the switch)
+      uint16_t* dst = T.mc_stage ? T.stage[r] + (long long)o * E : T.stage[o] + (long long)r * E;
       // four independent 32-byte loads per thread before the first store: the loop is bound by load latency otherwise
       const long long stride = (long long)blockDim.x * VEC;
       for (long long l0 = lo + threadIdx.x * VEC; l0 < hi; l0 += 4 * stride) {
@@ -218,7 +220,12 @@ __global__ void __launch_bounds__(256) push_sync_kernel(const __grid_constant__ 
     float* mom = T.mom[o];
     for (long long l = lo + threadIdx.x * VEC; l < hi; l += blockDim.x * VEC) {
       F8 g = {};
-      for (int s = 0; s < W + T.n_extra; ++s) {
+      if (T.mc_stage) {
+        // ONE load: the switch adds the W replicas (fp32 accumulation) and returns the sum.  A dropped source cannot be
+        // left out of an in-switch sum; the sticky error bit raised above already makes the host restart the job.
+        acc_f16x8(g, multimem_ld_reduce_f16x8(T.mc_stage + (long long)o * E + l), 1.0f);
+      }
+      for (int s = 0; s < W + T.n_extra && !T.mc_stage; ++s) {
         if (!((present >> s) & 1u)) continue;
         if (compress_fp16) {
           acc_f16x8(g, ld_v4(T.stage[o] + (long long)s * E + l), 1.0f);
@@ -668,12 +675,14 @@ static int check_tables(const DpsTables* T) {
   if (T->block_elems <= 0 || T->block_elems % 8 != 0 || (T->block_elems & (T->block_elems - 1)))
     DPS_FAIL(1, "block_elems must be a power of two >= 8");
   if (T->shard_elems <= 0 || T->shard_elems % T->block_elems != 0) DPS_FAIL(1, "shard_elems must be a multiple of block_elems");
+  if (T->mc_stage && T->n_extra) DPS_FAIL(1, "the NVLS reduction sums every replica: no extra (remote) sources");
   return 0;
 }
 
 DPS_API int dps_push_sync(const DpsTables* T, unsigned step, float lr, float momentum, float weight_decay,
                           int compress_fp16, int ctas, unsigned long long timeout_ns, void* stream) {
   if (int e = check_tables(T)) return e;
+  if (T->mc_stage && !compress_fp16) DPS_FAIL(1, "the NVLS reduction needs the fp16 wire format");
   if (T->n_extra > 0 && T->rank_lo < T->world)
     remote_gate_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, step, (uint32_t)ctas);
   push_sync_kernel<<<ctas, 256, 0, (cudaStream_t)stream>>>(*T, step, lr, momentum, weight_decay, compress_fp16,
@@ -689,6 +698,7 @@ DPS_API int dps_push_segment(const DpsTables* T, unsigned step, float lr, float 
   if (seg_lo < 0 || seg_hi > T->shard_elems || seg_lo > seg_hi || seg_lo % 8 || seg_hi % 8)
     DPS_FAIL(1, "push_segment: bad range [%lld, %lld)", seg_lo, seg_hi);
   if (!(phases & 3)) DPS_FAIL(1, "push_segment: phases must select SEND (1) and/or REDUCE (2)");
+  if (T->mc_stage && !compress_fp16) DPS_FAIL(1, "the NVLS reduction needs the fp16 wire format");
   if (ctas < 1) DPS_FAIL(1, "push_segment: ctas must be positive");
   if ((phases & 2) && T->n_extra > 0 && T->rank_lo < T->world)
     remote_gate_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(*T, step, arrivals_per_step);

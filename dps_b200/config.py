@@ -76,6 +76,7 @@ class Config:
     async_server_period_us: int = 100     # pause between two scans of the arrival ring by the server thread
     staleness_policy: str = "reference"   # 'reference' | 'world' (bound + W-1) | 'batch' (one version per drained batch)
     nvls: str = "off"                     # pull broadcast through an NVLS multicast window: 'off' | 'auto' | 'on'
+    nvls_reduce: bool = False             # sync push: sources stage locally, owners sum the replicas with multimem.ld_reduce
     serve_port: Optional[int] = None      # device path: rank 0 also serves the gRPC contract on this port (0 = any free)
     remote_slots: int = 0                 # source slots for remote workers attached through that door (sync mode)
     # ---- outputs -----------------------------------------------------------
@@ -177,6 +178,8 @@ def add_common_args(p: argparse.ArgumentParser) -> None:
     p.add_argument("--nvls", choices=["off", "auto", "on"], default="off",
                    help="on-box job: pull broadcast through an NVLS multicast window (one multimem.st per vector "
                         "instead of W peer stores); auto = when the box supports it")
+    p.add_argument("--nvls-reduce", action="store_true", default=None,
+                   help="on-box sync job (with --nvls auto|on): in-switch reduction of the push (multimem.ld_reduce)")
     p.add_argument("--serve-port", type=int, default=None,
                    help="on-box job: rank 0 also serves the gRPC contract on this port (remote / CPU workers)")
     p.add_argument("--remote-slots", type=int, default=0,

@@ -43,7 +43,7 @@ class DpsTables(C.Structure):
         ("ring", _PtrArray), ("wbf16", _PtrArray), ("small", _PtrArray), ("pub", _PtrArray),
         ("pubsmall", _PtrArray), ("flags", _PtrArray),
         ("step_ctr", _P), ("lr_ptr", _P),
-        ("mc_wbf16", _P), ("mc_small", _P),
+        ("mc_wbf16", _P), ("mc_small", _P), ("mc_stage", _P),
     ]
 
 

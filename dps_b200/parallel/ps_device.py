@@ -57,9 +57,14 @@ class DevicePS:
         if world + self.n_extra > L.MAX_RANKS:
             raise ValueError(f"workers + remote_slots must be <= {L.MAX_RANKS}")
 
+        # NVLS reduction of the sync push (Config.nvls_reduce, needs nvls != 'off'): the staging area moves into the
+        # multicast arena, [owner][E] fp16 on every rank; sources store into their own replica, owners multimem.ld_reduce
+        want_mc_stage = bool(cfg.nvls_reduce) and cfg.mode == "sync"
+        if want_mc_stage and (self.n_extra or not self.compress):
+            raise ValueError("nvls_reduce sums every replica in the switch: fp16 wire format and no remote_slots")
         spec = ArenaSpec()
         spec.add("flags", L.FLAG_WORDS * 4)
-        spec.add("stage", (world + self.n_extra) * self.E * (2 if self.compress else 4))
+        stage_bytes = (world + self.n_extra) * self.E * (2 if self.compress else 4)
         if self.n_extra:
             spec.add("master", self.E * 4)
         # NVLS (Config.nvls): the two pull destinations live in a multicast-bound arena instead, so the owner's
@@ -73,6 +78,8 @@ class DevicePS:
                 mspec = ArenaSpec()
                 mspec.add("wbf16", self.total * 2)
                 mspec.add("small", max(self.n_small, 8) * 4)
+                if want_mc_stage:
+                    mspec.add("stage", stage_bytes)
                 self.mc = MulticastArena(rank, world, device_index, mspec, group=group)
                 if not self.mc.mc_base:
                     raise RuntimeError("no multicast window could be mapped")
@@ -86,6 +93,12 @@ class DevicePS:
         if not want_mc:
             spec.add("wbf16", self.total * 2)
             spec.add("small", max(self.n_small, 8) * 4)
+        if want_mc_stage and not want_mc:
+            if cfg.nvls == "off":
+                raise ValueError("nvls_reduce needs nvls = 'auto' or 'on'")
+            want_mc_stage = False                            # 'auto' on a box without multicast: per-peer push
+        if not want_mc_stage:
+            spec.add("stage", stage_bytes)
         if self.is_async:
             spec.add("ring", self.R * self.E * 2)
             spec.add("pub", self.E * 2)
@@ -93,7 +106,9 @@ class DevicePS:
         self.fabric = Fabric(rank, world, device_index, spec, emulate=emulate, group=group)
         self.lib = self.fabric.lib
         self.nvls = bool(self.mc is not None and self.mc.mc_base)
+        self.nvls_reduce = bool(self.nvls and want_mc_stage)
         warena = self.mc if self.mc is not None else self.fabric      # where wbf16 / small live
+        sarena = self.mc if self.nvls_reduce else self.fabric         # where the sync staging area lives
 
         # local-only buffers
         self.local = list(self.fabric.local_ranks())
@@ -117,7 +132,7 @@ class DevicePS:
         t.shard_elems, t.n_small = self.E, self.n_small
         t.rank_lo, t.rank_hi = (0, world) if emulate else (rank, rank + 1)
         for r in range(world):
-            t.stage[r] = self.fabric.ptr(r, "stage")
+            t.stage[r] = sarena.ptr(r, "stage")
             t.wbf16[r] = warena.ptr(r, "wbf16")
             t.small[r] = warena.ptr(r, "small")
             t.flags[r] = self.fabric.ptr(r, "flags")
@@ -131,6 +146,8 @@ class DevicePS:
             t.mom[r] = self.mom[r].data_ptr()
         if self.nvls:
             t.mc_wbf16, t.mc_small = self.mc.mc_ptr("wbf16"), self.mc.mc_ptr("small")
+        if self.nvls_reduce:
+            t.mc_stage = self.mc.mc_ptr("stage")
         # device-resident round counters + learning rate (graph replay needs no baked-in step / lr)
         self.step_ctr = torch.zeros(4, dtype=torch.int32, device=dev)
         self.lr_dev = torch.full((1,), float(cfg.lr), dtype=torch.float32, device=dev)

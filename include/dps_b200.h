@@ -94,6 +94,11 @@ typedef struct DpsTables {
    * NULL = per-peer stores. */
   uint16_t* mc_wbf16;
   float* mc_small;
+  /* Optional NVLS reduction of the sync push: when non-NULL, `stage` lives in the multicast-bound arena, laid out
+   * [owner][E] on EVERY rank; SEND writes the source's fp16 tiles into its OWN replica (no peer stores) and the owner's
+   * REDUCE reads mc_stage + owner*E + l with multimem.ld_reduce, which returns the sum over all W replicas.  fp16 wire
+   * only, no extra sources (n_extra == 0). */
+  uint16_t* mc_stage;
 } DpsTables;
 
 const char* dps_last_error(void);

@@ -82,4 +82,4 @@ def test_ctypes_mirror_of_the_pointer_tables_matches_the_library():
         pytest.skip("native library not built")
     assert L.lib().dps_tables_size() == ctypes.sizeof(L.DpsTables)
     names = [f[0] for f in L.DpsTables._fields_]
-    assert names[-2:] == ["mc_wbf16", "mc_small"] and names.index("flags") < names.index("step_ctr")
+    assert names[-3:] == ["mc_wbf16", "mc_small", "mc_stage"] and names.index("flags") < names.index("step_ctr")
