@@ -74,6 +74,24 @@ def test_pull_through_the_nvls_multicast_window(mode, tmp_path):
         assert res["torn_pulls"] == [0, 0] and res["versions_monotone"] == [1, 1]
 
 
+def test_sync_push_reduced_in_the_switch(tmp_path):
+    """Config.nvls_reduce: sources stage their fp16 tiles into their OWN replica of the multicast-bound staging arena
+    and the owners sum the replicas with multimem.ld_reduce.  The first step must still equal the mean-gradient step
+    (the in-switch sum returns fp16: 2^-11 relative on the mean gradient) and the replicas must stay identical."""
+    if _ngpu() < 2:
+        pytest.skip("needs 2 GPUs")
+    out = tmp_path / "res_nvls_reduce.json"
+    r = _torchrun(2, [os.path.join(ROOT, "bench_tools", "mgpu_check.py"), "sync", str(out), "10"], port=29681,
+                  env={"DPS_NVLS": "auto", "DPS_NVLS_REDUCE": "1"})
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-3000:]
+    res = json.loads(out.read_text())
+    if not res["nvls_reduce"]:
+        pytest.skip("no NVLS multicast on this box: " + r.stderr[-300:])
+    assert res["error_bits"] == [0, 0] and res["replicas_equal"] and res["finite"]
+    assert res["versions"] == [10, 10]
+    assert res["max_abs_diff_vs_single_process_mean_step"] < 2e-3
+
+
 @pytest.mark.skipif(_ngpu() < 2, reason="needs >= 2 GPUs")
 def test_injected_rank_death_is_recovered_from_the_last_checkpoint(tmp_path):
     """rank 1's process dies at step 12 of 30 (os._exit, nothing cleaned up).  The supervising launcher
