@@ -15,7 +15,7 @@ from __future__ import annotations
 import argparse
 import dataclasses
 import os
-from dataclasses import dataclass, field
+from dataclasses import dataclass
 from typing import Any, Dict, Optional, Sequence
 
 # Env-var names used by the reference's container definitions.

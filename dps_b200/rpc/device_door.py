@@ -24,7 +24,7 @@ from __future__ import annotations
 import threading
 import time
 from concurrent import futures
-from typing import Dict, List, Optional
+from typing import Dict, List
 
 import grpc
 import numpy as np

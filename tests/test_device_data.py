@@ -1,6 +1,5 @@
 """Device-resident input pipeline (csrc/data.cu, dps_b200/utils/device_data.py) against a plain fp32 host restatement
 of the reference's transform stack (reference: src/workers/worker.py:146-158)."""
-import numpy as np
 import pytest
 import torch
 

@@ -3,7 +3,6 @@ this framework's CPU worker talk to the GPU shards of a running job (reference: 
 src/parameter_server/server.py:190-318)."""
 import pickle
 import threading
-import time
 
 import numpy as np
 import pytest

@@ -1,8 +1,6 @@
 """The supervising launcher (dps_b200.launch.supervise): restart policy of the on-box job, exercised without GPUs through
 a fake `run_once` (reference: the "automatic failover" the README claims, README.md:51, which ECS task restarts with a
 fresh out-of-range worker id never delivered)."""
-import os
-
 from dps_b200 import launch as LN
 from dps_b200.config import parse_server_cli
 
